@@ -1,0 +1,247 @@
+// oracle/pt_oracle.cpp -- TEST INFRASTRUCTURE ONLY (never linked into the product; only tests/, smoke() and
+// bench.py's cpu_baseline leg may load it).
+//
+// CPU restatement of the hot path as ONE scalar loop per camera sample, in the shape of the reference's own
+// control flow:
+//     Tiled::compute        renderer.h:626-691   pixel/sample loop, framebuffer[j][i] += de_nan(col)
+//     NEEIterative::color   integrator.h:176-339 bounce loop: hit -> scatter/emitted -> NEE x light_samples ->
+//                                                generate -> Russian roulette -> throughput
+//     RecursivePT::color    integrator.h:29-72
+//     World::hit            world.h:17-20        (flat BVH here)
+// It is built from the same `__host__ __device__` math headers as the CUDA kernels (pathtrace_b200/csrc/device/
+// pt_*.h, compiled here by g++ -ffp-contract=off) and draws from the same Philox stream keyed by
+// (pixel, sample, bounce, stage), so a GPU render and this loop agree per SAMPLE, not just statistically: it
+// checks the wavefront plumbing (queues, compaction, sorting, batching, accumulation).  It is NOT the
+// independent oracle: that is oracle/_ref/ref_driver, the unmodified reference, against which this restatement
+// itself is pinned statistically on the CPU (tests/test_oracle_vs_reference.py) and the hit routine ray by ray.
+// PARITY PIN: hit routine -- exact comparison with the reference on fixed ray batches; render -- statistical
+// (clamped per-pixel z-scores) against the reference's integrator->color; no upstream golden vectors exist.
+#include "../include/b200pt.h"
+#include "../pathtrace_b200/csrc/device/pt_shade.h"
+#include "../pathtrace_b200/csrc/host/flat_scene.h"
+#include "../pathtrace_b200/csrc/host/scene_pack.h"
+
+#include <atomic>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+using namespace b200pt;
+using namespace pt;
+
+namespace {
+
+thread_local std::string g_err;
+
+struct OracleScene {
+    FlatScene flat;
+    PackedScene packed;
+    PtSceneView view;
+};
+
+struct SampleCounts {
+    long ext = 0, shadow = 0, reference = 0;
+};
+
+RenderParams make_params(const b200pt_config &c)
+{
+    RenderParams rp{};
+    rp.width = c.width;
+    rp.height = c.height;
+    rp.integrator = c.integrator;
+    rp.max_bounces = c.max_bounces;
+    rp.light_samples = c.integrator == B200PT_INTEGRATOR_INEEPT ? c.light_samples : 0;
+    rp.russian_roulette = c.russian_roulette;
+    rp.only_direct = c.only_direct_illumination;
+    rp.normal_offset = c.normal_offset;
+    rp.seed_lo = (uint32_t)(c.seed & 0xffffffffull);
+    rp.seed_hi = (uint32_t)(c.seed >> 32);
+    return rp;
+}
+
+// one camera sample = one call of integrator->color (renderer.h:648-670)
+V3 sample_color(const PtSceneView &s, const RenderParams &rp, uint32_t pixel, uint32_t sample, SampleCounts &cnt)
+{
+    RngKey key;
+    key.seed_lo = rp.seed_lo;
+    key.seed_hi = rp.seed_hi;
+    key.pixel = pixel;
+    key.sample = sample;
+    F4 r = rng4(key, stage_word(0, RNG_CAMERA, 0), 0);
+    int j = pixel / rp.width, i = pixel - j * rp.width;
+    float u = (float)(i + (double)r.x) / (float)rp.width;
+    float v = (float)(j + (double)r.y) / (float)rp.height;
+    PathVertexIn in;
+    camera_ray(s.cam, u, v, r.z, r.w, in.o, in.d);
+    in.beta = v3(1.f, 1.f, 1.f);
+    in.attenuation = v3(0.f, 0.f, 0.f);
+    in.last_bsdf_pdf = -1.f;
+    V3 sum = v3(0.f, 0.f, 0.f);
+    const bool nee = rp.integrator == B200PT_INTEGRATOR_INEEPT;
+    const int n_bounces = nee ? rp.max_bounces : rp.max_bounces + 1;
+    for (int b = 0; b < n_bounces; b++) {
+        MediumRng mr;
+        mr.key = key;
+        mr.stage = stage_word(b, RNG_EXT_MEDIUM, 0);
+        mr.xi = -1.f;
+        Hit rec;
+        cnt.ext++;
+        if (nee || b > 0)
+            cnt.reference++;
+        if (!trace_closest<false>(s, in.o, in.d, 0.001f, PT_FLT_MAX, mr, rec, nullptr)) {
+            sum += shade_miss(s, in.d, in.beta);
+            break;
+        }
+        F4 rnd = rng4(key, stage_word(b, RNG_SHADE, 0), 0);
+        PathVertexOut out;
+        // `attenuation` only survives from the previous vertex when a light is hit (material.h:187-191)
+        PathVertexIn vin = in;
+        if (s.mats[meta_material(s.inst[rec.inst].meta)].kind != B200PT_MAT_DIFFUSE_LIGHT)
+            vin.attenuation = v3(0.f, 0.f, 0.f);
+        if (nee)
+            shade_hit_ineept(s, rp, vin, rec, rnd, out);
+        else
+            shade_hit_rpt(s, rp, vin, rec, b, rnd, out);
+        sum += out.add;
+        if (nee)
+            cnt.reference += rp.light_samples;
+        if (out.want_nee) {
+            V3 light = v3(0.f, 0.f, 0.f);
+            for (int k = 0; k < rp.light_samples; k++) {
+                light += nee_sample<false>(s, rp, key, b, k, rec.p, rec.n, out.mat_kind, out.W, nullptr);
+                cnt.shadow++;
+            }
+            sum += light / (float)rp.light_samples;
+        }
+        if (!out.cont)
+            break;
+        in.o = out.o;
+        in.d = out.d;
+        in.beta = out.beta;
+        in.attenuation = out.attenuation;
+        in.last_bsdf_pdf = out.last_bsdf_pdf;
+    }
+    return sum;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *pt_oracle_last_error(void) { return g_err.c_str(); }
+
+void *pt_oracle_scene_create(const char *scene_json, int film_w, int film_h)
+{
+    try {
+        OracleScene *sc = new OracleScene;
+        sc->flat = compile_scene(Json::parse(scene_json), film_w, film_h);
+        sc->packed = pack_scene(sc->flat);
+        sc->view = sc->packed.host_view(sc->flat);
+        return sc;
+    } catch (const std::exception &e) {
+        g_err = e.what();
+        return nullptr;
+    }
+}
+
+void pt_oracle_scene_destroy(void *scene) { delete (OracleScene *)scene; }
+
+// World::hit for n rays; same contract as b200pt_trace_batch
+int pt_oracle_trace(void *scene, const float *rays, size_t n, const float *medium_xi, b200pt_hit *hits)
+{
+    OracleScene *sc = (OracleScene *)scene;
+    for (size_t i = 0; i < n; i++) {
+        const float *q = rays + i * 8;
+        MediumRng mr;
+        mr.key.seed_lo = mr.key.seed_hi = 0;
+        mr.key.pixel = (uint32_t)(i & 0xffffffffull);
+        mr.key.sample = (uint32_t)(i >> 32);
+        mr.stage = stage_word(0, RNG_BATCH_MEDIUM, 0);
+        mr.xi = medium_xi ? medium_xi[i] : -1.f;
+        Hit h;
+        bool ok = trace_closest<false>(sc->view, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7], mr, h, nullptr);
+        b200pt_hit &o = hits[i];
+        memset(&o, 0, sizeof(o));
+        o.instance = -1;
+        if (ok) {
+            o.instance = h.inst;
+            o.t = h.t;
+            o.p[0] = h.p.x, o.p[1] = h.p.y, o.p[2] = h.p.z;
+            o.n[0] = h.n.x, o.n[1] = h.n.y, o.n[2] = h.n.z;
+            o.u = h.u;
+            o.v = h.v;
+        }
+    }
+    return 0;
+}
+
+// The render loop.  rgb_sums: H x W x 3 float32 sums, row 0 = image bottom (Renderer::framebuffer).
+// clamped_sum / clamped_sumsq: optional parity statistics (config.stats_clamp).  counts[3]: extension rays,
+// shadow rays, reference-accounting rays.  pixel_begin/pixel_end restrict the work to a pixel range (timing
+// samples); threads = worker count (rows are interleaved; results do not depend on it).
+int pt_oracle_render(void *scene, const b200pt_config *config, float *rgb_sums, float *clamped_sum, float *clamped_sumsq,
+                     int64_t counts[3], int threads, int64_t pixel_begin, int64_t pixel_end)
+{
+    OracleScene *sc = (OracleScene *)scene;
+    const b200pt_config &c = *config;
+    RenderParams rp = make_params(c);
+    const int64_t npix = (int64_t)c.width * c.height;
+    if (pixel_end <= 0 || pixel_end > npix)
+        pixel_end = npix;
+    if (pixel_begin < 0)
+        pixel_begin = 0;
+    if (threads < 1)
+        threads = 1;
+    std::atomic<long> t_ext{0}, t_shadow{0}, t_ref{0};
+    std::atomic<int64_t> next{pixel_begin};
+    const int64_t chunk = 256;
+    auto worker = [&]() {
+        SampleCounts cnt;
+        while (true) {
+            int64_t p0 = next.fetch_add(chunk);
+            if (p0 >= pixel_end)
+                break;
+            int64_t p1 = p0 + chunk < pixel_end ? p0 + chunk : pixel_end;
+            for (int64_t pix = p0; pix < p1; pix++) {
+                float acc[3] = {0, 0, 0}, cs[3] = {0, 0, 0}, cq[3] = {0, 0, 0};
+                for (int sidx = 0; sidx < c.samples; sidx++) {
+                    V3 col = sample_color(sc->view, rp, (uint32_t)pix, (uint32_t)(c.sample_offset + sidx), cnt);
+                    float x[3] = {is_nan(col.x) ? 0.f : col.x, is_nan(col.y) ? 0.f : col.y, is_nan(col.z) ? 0.f : col.z};
+                    for (int k = 0; k < 3; k++) {
+                        acc[k] += x[k];
+                        if (c.stats_clamp > 0.f) {
+                            float cx = x[k] < c.stats_clamp ? x[k] : c.stats_clamp;
+                            cs[k] += cx;
+                            cq[k] += cx * cx;
+                        }
+                    }
+                }
+                for (int k = 0; k < 3; k++) {
+                    rgb_sums[3 * pix + k] = acc[k];
+                    if (clamped_sum)
+                        clamped_sum[3 * pix + k] = cs[k];
+                    if (clamped_sumsq)
+                        clamped_sumsq[3 * pix + k] = cq[k];
+                }
+            }
+        }
+        t_ext += cnt.ext;
+        t_shadow += cnt.shadow;
+        t_ref += cnt.reference;
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < threads; t++)
+        pool.emplace_back(worker);
+    worker();
+    for (auto &t : pool)
+        t.join();
+    if (counts) {
+        counts[0] = t_ext;
+        counts[1] = t_shadow;
+        counts[2] = t_ref;
+    }
+    return 0;
+}
+
+} // extern "C"

@@ -1,0 +1,619 @@
+// capi.cu -- the extern "C" layer (include/b200pt.h): scene upload, the render lifecycle that stands in for the
+// reference's Renderer (renderer.h:114-150: start_render / sync_progress / is_done / finalize) and the
+// closest-hit parity entry point.  Everything below the ABI runs on the GPU; there is no CPU fallback.
+#include "../../include/b200pt.h"
+#include "device/wavefront.cuh"
+#include "host/bvh_build.h"
+#include "host/config.h"
+#include "host/flat_scene.h"
+#include "host/scene_pack.h"
+
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <memory>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+using namespace b200pt;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string &msg)
+{
+    g_last_error = msg;
+    return code;
+}
+
+struct CudaError : std::runtime_error {
+    explicit CudaError(const std::string &m) : std::runtime_error(m) {}
+};
+struct NoDevice : std::runtime_error {
+    explicit NoDevice(const std::string &m) : std::runtime_error(m) {}
+};
+
+#define CK(expr)                                                                                                       \
+    do {                                                                                                               \
+        cudaError_t e_ = (expr);                                                                                       \
+        if (e_ != cudaSuccess)                                                                                         \
+            throw CudaError(std::string(#expr) + ": " + cudaGetErrorString(e_));                                       \
+    } while (0)
+
+template <typename F> int guarded(F &&f)
+{
+    try {
+        f();
+        return B200PT_OK;
+    } catch (const NoDevice &e) {
+        return fail(B200PT_ERR_NO_DEVICE, e.what());
+    } catch (const CudaError &e) {
+        return fail(B200PT_ERR_CUDA, e.what());
+    } catch (const std::exception &e) {
+        return fail(B200PT_ERR_INVALID, e.what());
+    }
+}
+
+template <typename T> T *dev_upload(const std::vector<T> &v)
+{
+    T *d = nullptr;
+    size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
+    CK(cudaMalloc(&d, bytes));
+    if (!v.empty())
+        CK(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return d;
+}
+
+void select_device(int device)
+{
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        throw NoDevice(std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                       " (this backend has no CPU fallback)");
+    if (device < 0 || device >= count)
+        throw std::runtime_error("device ordinal out of range");
+    CK(cudaSetDevice(device));
+}
+
+} // namespace
+
+struct b200pt_scene {
+    FlatScene flat;
+    PackedScene packed;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    pt::PtSceneView view{};
+    std::vector<void *> allocations;
+    int n_media = 0;
+
+    ~b200pt_scene()
+    {
+        if (device >= 0)
+            cudaSetDevice(device);
+        for (void *p : allocations)
+            cudaFree(p);
+        if (stream)
+            cudaStreamDestroy(stream);
+    }
+};
+
+namespace {
+
+void upload_scene(b200pt_scene &sc)
+{
+    sc.packed = pack_scene(sc.flat);
+    sc.n_media = sc.packed.n_media;
+    sc.view = sc.packed.host_view(sc.flat); // host pointers, replaced below when a device is attached
+    if (sc.device < 0)
+        return; // host-only handle: description and BVH can be inspected, nothing can be traced
+    select_device(sc.device);
+    CK(cudaStreamCreateWithFlags(&sc.stream, cudaStreamNonBlocking));
+    auto keep = [&](auto *p) {
+        sc.allocations.push_back((void *)p);
+        return p;
+    };
+    pt::PtSceneView &v = sc.view;
+    v.nodes = keep(dev_upload(sc.packed.bvh.nodes));
+    v.inst = keep(dev_upload(sc.packed.inst));
+    v.fwd = keep(dev_upload(sc.packed.fwd));
+    v.mats = keep(dev_upload(sc.flat.materials));
+    v.tex = keep(dev_upload(sc.flat.textures));
+    v.lights = keep(dev_upload(sc.flat.lights));
+    v.perlin_ranvec = keep(dev_upload(sc.packed.perlin_ranvec));
+    v.perlin_perm = keep(dev_upload(sc.packed.perlin_perm));
+}
+
+void need_device(const b200pt_scene *sc)
+{
+    if (sc->device < 0)
+        throw NoDevice("scene handle was created host-only (device = -1); this backend has no CPU fallback");
+    select_device(sc->device);
+}
+
+} // namespace
+
+struct b200pt_render {
+    b200pt_scene *scene = nullptr;
+    b200pt_config cfg{};
+    pt::RenderParams rp{};
+    pt::Wavefront wf{};
+    pt::Film film{};
+    pt::LaunchCfg lc{};
+    std::vector<void *> allocations;
+    float *d_lum = nullptr;   // [2]
+    uint8_t *d_rgb = nullptr; // H*W*3
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int batch_samples = 1;
+    int batches_total = 0, batches_done = 0;
+    int n_rows = 0;
+    double seconds = 0.0;
+    int64_t spp_done = 0;
+
+    ~b200pt_render()
+    {
+        if (scene)
+            cudaSetDevice(scene->device);
+        for (void *p : allocations)
+            cudaFree(p);
+        if (ev0)
+            cudaEventDestroy(ev0);
+        if (ev1)
+            cudaEventDestroy(ev1);
+    }
+};
+
+namespace {
+
+template <typename T> T *render_alloc(b200pt_render &r, size_t count, bool zero = false)
+{
+    T *p = nullptr;
+    CK(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
+    r.allocations.push_back(p);
+    if (zero)
+        CK(cudaMemset(p, 0, std::max<size_t>(count, 1) * sizeof(T)));
+    return p;
+}
+
+void enqueue_batch(b200pt_render &r)
+{
+    cudaStream_t st = r.scene->stream;
+    const pt::PtSceneView &s = r.scene->view;
+    CK(cudaMemsetAsync(r.wf.counters, 0, sizeof(int32_t) * pt::CNT_ROW * r.n_rows, st));
+    pt::launch_raygen(s, r.rp, r.wf, r.lc, st);
+    const bool nee = r.cfg.integrator == B200PT_INTEGRATOR_INEEPT;
+    const int n_bounces = nee ? r.cfg.max_bounces : r.cfg.max_bounces + 1;
+    for (int b = 0; b < n_bounces; b++) {
+        pt::launch_extend(s, r.rp, r.wf, b, r.lc, st);
+        for (int k = 0; k < pt::SK_COUNT; k++)
+            pt::launch_shade(s, r.rp, r.wf, b, k, r.lc, st);
+        if (nee)
+            pt::launch_nee(s, r.rp, r.wf, b, r.lc, st);
+    }
+    pt::launch_accumulate(r.rp, r.wf, r.film, n_bounces, st);
+    CK(cudaGetLastError());
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------------------------------
+
+extern "C" {
+
+const char *b200pt_last_error(void) { return g_last_error.c_str(); }
+
+const char *b200pt_version(void) { return "b200pt 0.1 (sm_100a, wavefront)"; }
+
+int b200pt_config_from_json(const char *config_json, b200pt_config *out, char *scene_path, size_t scene_cap,
+                            char *ppm_path, size_t ppm_cap)
+{
+    if (!config_json || !out)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    return guarded([&] {
+        ParsedConfig pc = parse_config(Json::parse(config_json));
+        *out = pc.config;
+        if (scene_path && scene_cap) {
+            strncpy(scene_path, pc.scene_path.c_str(), scene_cap - 1);
+            scene_path[scene_cap - 1] = 0;
+        }
+        if (ppm_path && ppm_cap) {
+            strncpy(ppm_path, pc.ppm_output_path.c_str(), ppm_cap - 1);
+            ppm_path[ppm_cap - 1] = 0;
+        }
+    });
+}
+
+int b200pt_scene_create_from_json(const char *scene_json, int32_t film_width, int32_t film_height, int32_t device,
+                                  b200pt_scene **out)
+{
+    if (!scene_json || !out || film_width <= 0 || film_height <= 0)
+        return fail(B200PT_ERR_INVALID, "bad argument");
+    *out = nullptr;
+    return guarded([&] {
+        std::unique_ptr<b200pt_scene> sc(new b200pt_scene);
+        sc->device = device;
+        sc->flat = compile_scene(Json::parse(scene_json), film_width, film_height);
+        upload_scene(*sc);
+        *out = sc.release();
+    });
+}
+
+int b200pt_scene_create(const b200pt_scene_desc *desc, int32_t device, b200pt_scene **out)
+{
+    if (!desc || !out)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    *out = nullptr;
+    return guarded([&] {
+        std::unique_ptr<b200pt_scene> sc(new b200pt_scene);
+        sc->device = device;
+        sc->flat = FlatScene::from_desc(*desc);
+        upload_scene(*sc);
+        *out = sc.release();
+    });
+}
+
+int b200pt_scene_get_desc(const b200pt_scene *scene, b200pt_scene_desc *out)
+{
+    if (!scene || !out)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    *out = scene->flat.desc();
+    return B200PT_OK;
+}
+
+int b200pt_scene_bvh_info(const b200pt_scene *scene, int32_t *n_nodes, int32_t *max_depth, float bounds[6])
+{
+    if (!scene)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    if (n_nodes)
+        *n_nodes = (int32_t)scene->packed.bvh.nodes.size();
+    if (max_depth)
+        *max_depth = scene->packed.bvh.max_depth;
+    if (bounds)
+        memcpy(bounds, scene->packed.bvh.bounds, sizeof(float) * 6);
+    return B200PT_OK;
+}
+
+void b200pt_scene_destroy(b200pt_scene *scene) { delete scene; }
+
+int b200pt_trace_batch_device(b200pt_scene *scene, const void *d_rays, size_t n, const void *d_medium_xi, void *d_hits,
+                              int32_t repeat, float *ms)
+{
+    if (!scene || (!d_rays && n))
+        return fail(B200PT_ERR_INVALID, "null argument");
+    return guarded([&] {
+        need_device(scene);
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (ms) {
+            CK(cudaEventCreate(&e0));
+            CK(cudaEventCreate(&e1));
+            CK(cudaEventRecord(e0, scene->stream));
+        }
+        for (int i = 0; i < (repeat < 1 ? 1 : repeat); i++)
+            pt::launch_trace_batch(scene->view, (const float *)d_rays, n, (const float *)d_medium_xi,
+                                   (b200pt_hit *)d_hits, nullptr, scene->stream);
+        CK(cudaGetLastError());
+        if (ms) {
+            CK(cudaEventRecord(e1, scene->stream));
+            CK(cudaEventSynchronize(e1));
+            CK(cudaEventElapsedTime(ms, e0, e1));
+            cudaEventDestroy(e0);
+            cudaEventDestroy(e1);
+        }
+    });
+}
+
+int b200pt_trace_batch(b200pt_scene *scene, const float *rays, size_t n, const float *medium_xi, b200pt_hit *hits)
+{
+    if (!scene || ((!rays || !hits) && n))
+        return fail(B200PT_ERR_INVALID, "null argument");
+    return guarded([&] {
+        need_device(scene);
+        if (n == 0)
+            return;
+        float *d_rays = nullptr, *d_xi = nullptr;
+        b200pt_hit *d_hits = nullptr;
+        struct Guard {
+            float *&a, *&b;
+            b200pt_hit *&c;
+            ~Guard()
+            {
+                cudaFree(a);
+                cudaFree(b);
+                cudaFree(c);
+            }
+        } guard{d_rays, d_xi, d_hits};
+        CK(cudaMalloc(&d_rays, n * 8 * sizeof(float)));
+        CK(cudaMalloc(&d_hits, n * sizeof(b200pt_hit)));
+        CK(cudaMemcpyAsync(d_rays, rays, n * 8 * sizeof(float), cudaMemcpyHostToDevice, scene->stream));
+        if (medium_xi) {
+            CK(cudaMalloc(&d_xi, n * sizeof(float)));
+            CK(cudaMemcpyAsync(d_xi, medium_xi, n * sizeof(float), cudaMemcpyHostToDevice, scene->stream));
+        }
+        pt::launch_trace_batch(scene->view, d_rays, n, d_xi, d_hits, nullptr, scene->stream);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(hits, d_hits, n * sizeof(b200pt_hit), cudaMemcpyDeviceToHost, scene->stream));
+        CK(cudaStreamSynchronize(scene->stream));
+    });
+}
+
+int b200pt_trace_count(b200pt_scene *scene, const float *rays, size_t n, uint64_t counts[3])
+{
+    if (!scene || (!rays && n) || !counts)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    return guarded([&] {
+        need_device(scene);
+        counts[0] = counts[1] = counts[2] = 0;
+        if (n == 0)
+            return;
+        float *d_rays = nullptr;
+        unsigned long long *d_counts = nullptr;
+        struct Guard {
+            float *&a;
+            unsigned long long *&b;
+            ~Guard()
+            {
+                cudaFree(a);
+                cudaFree(b);
+            }
+        } guard{d_rays, d_counts};
+        CK(cudaMalloc(&d_rays, n * 8 * sizeof(float)));
+        CK(cudaMalloc(&d_counts, 3 * sizeof(unsigned long long)));
+        CK(cudaMemsetAsync(d_counts, 0, 3 * sizeof(unsigned long long), scene->stream));
+        CK(cudaMemcpyAsync(d_rays, rays, n * 8 * sizeof(float), cudaMemcpyHostToDevice, scene->stream));
+        pt::launch_trace_batch(scene->view, d_rays, n, nullptr, nullptr, d_counts, scene->stream);
+        CK(cudaGetLastError());
+        unsigned long long h[3];
+        CK(cudaMemcpyAsync(h, d_counts, sizeof(h), cudaMemcpyDeviceToHost, scene->stream));
+        CK(cudaStreamSynchronize(scene->stream));
+        counts[0] = h[0];
+        counts[1] = h[1];
+        counts[2] = h[2];
+    });
+}
+
+int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt_render **out)
+{
+    if (!scene || !config || !out)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    *out = nullptr;
+    return guarded([&] {
+        const b200pt_config &c = *config;
+        if (c.width <= 0 || c.height <= 0 || c.samples <= 0)
+            throw std::runtime_error("config: film size and samples must be positive");
+        if (c.integrator != B200PT_INTEGRATOR_INEEPT && c.integrator != B200PT_INTEGRATOR_RPT)
+            throw std::runtime_error("config: unsupported integrator");
+        if (c.max_bounces < 0 || c.max_bounces > 4096)
+            throw std::runtime_error("config: max_bounces out of range");
+        if (c.integrator == B200PT_INTEGRATOR_INEEPT && (c.light_samples < 0 || c.light_samples > 1024))
+            throw std::runtime_error("config: light_samples out of range");
+        if (c.device != scene->device)
+            throw std::runtime_error("config.device differs from the device the scene was uploaded to");
+        need_device(scene);
+        std::unique_ptr<b200pt_render> r(new b200pt_render);
+        r->scene = scene;
+        r->cfg = c;
+        const long long npix = (long long)c.width * c.height;
+        if (npix > (1ll << 30))
+            throw std::runtime_error("film too large");
+        // batch sizing: enough paths in flight to fill 148 SMs many times over, small enough to stay a few GB
+        const long long target_slots = 8ll << 20;
+        int bs = c.batch_samples > 0 ? c.batch_samples : (int)std::max<long long>(1, target_slots / npix);
+        bs = std::min(bs, c.samples);
+        while ((long long)bs * npix > (1ll << 30) && bs > 1)
+            bs--;
+        r->batch_samples = bs;
+        r->batches_total = (c.samples + bs - 1) / bs;
+        const size_t cap = (size_t)bs * (size_t)npix;
+
+        pt::RenderParams &rp = r->rp;
+        rp.width = c.width;
+        rp.height = c.height;
+        rp.integrator = c.integrator;
+        rp.max_bounces = c.max_bounces;
+        rp.light_samples = c.integrator == B200PT_INTEGRATOR_INEEPT ? c.light_samples : 0;
+        rp.russian_roulette = c.russian_roulette;
+        rp.only_direct = c.only_direct_illumination;
+        rp.normal_offset = c.normal_offset;
+        rp.seed_lo = (uint32_t)(c.seed & 0xffffffffull);
+        rp.seed_hi = (uint32_t)(c.seed >> 32);
+
+        pt::Wavefront &wf = r->wf;
+        wf.npix = (int32_t)npix;
+        wf.capacity = (int32_t)cap;
+        wf.ray_o = render_alloc<float4>(*r, cap);
+        wf.ray_d = render_alloc<float4>(*r, cap);
+        wf.beta = render_alloc<float4>(*r, cap);
+        wf.att = render_alloc<float4>(*r, cap);
+        wf.hit_p = render_alloc<float4>(*r, cap);
+        wf.hit_n = render_alloc<float4>(*r, cap);
+        wf.nee_w = render_alloc<float4>(*r, cap);
+        wf.sum = render_alloc<float4>(*r, cap);
+        for (int k = 0; k < 2; k++)
+            wf.q_ext[k] = render_alloc<int32_t>(*r, cap);
+        for (int k = 0; k < pt::SK_COUNT; k++)
+            wf.q_kind[k] = render_alloc<int32_t>(*r, cap);
+        wf.q_nee = render_alloc<int32_t>(*r, cap);
+        r->n_rows = c.max_bounces + 3;
+        wf.counters = render_alloc<int32_t>(*r, (size_t)pt::CNT_ROW * r->n_rows, true);
+        wf.ctl = render_alloc<pt::BatchCtl>(*r, 1, true);
+        pt::BatchCtl ctl{};
+        ctl.sample_base = c.sample_offset;
+        ctl.nsamp = bs;
+        ctl.remaining = c.samples - bs;
+        ctl.batch_samples = bs;
+        CK(cudaMemcpy(wf.ctl, &ctl, sizeof(ctl), cudaMemcpyHostToDevice));
+
+        r->film.accum = render_alloc<float4>(*r, (size_t)npix, true);
+        r->film.clamp = c.stats_clamp;
+        if (c.stats_clamp > 0.f) {
+            r->film.csum = render_alloc<float4>(*r, (size_t)npix, true);
+            r->film.csq = render_alloc<float4>(*r, (size_t)npix, true);
+        }
+        r->d_lum = render_alloc<float>(*r, 2, true);
+        r->d_rgb = render_alloc<uint8_t>(*r, (size_t)npix * 3);
+        CK(cudaEventCreate(&r->ev0));
+        CK(cudaEventCreate(&r->ev1));
+
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, scene->device));
+        r->lc.threads = 256;
+        r->lc.blocks = prop.multiProcessorCount * 8;
+        *out = r.release();
+    });
+}
+
+int b200pt_render_poll(b200pt_render *r, int32_t max_batches, b200pt_progress *progress)
+{
+    if (!r)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    return guarded([&] {
+        need_device(r->scene);
+        cudaStream_t st = r->scene->stream;
+        int todo = r->batches_total - r->batches_done;
+        if (max_batches > 0 && todo > max_batches)
+            todo = max_batches;
+        if (todo > 0) {
+            CK(cudaEventRecord(r->ev0, st));
+            for (int b = 0; b < todo; b++)
+                enqueue_batch(*r);
+            CK(cudaEventRecord(r->ev1, st));
+            CK(cudaEventSynchronize(r->ev1));
+            float ms = 0.f;
+            CK(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
+            r->seconds += ms * 1e-3;
+            r->batches_done += todo;
+        }
+        pt::BatchCtl ctl;
+        CK(cudaMemcpyAsync(&ctl, r->wf.ctl, sizeof(ctl), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        r->spp_done = (int64_t)(ctl.samples_done / (unsigned long long)r->wf.npix);
+        if (progress) {
+            progress->samples_done = (int64_t)ctl.samples_done;
+            progress->samples_total = (int64_t)r->cfg.samples * r->wf.npix;
+            progress->rays_extension = (int64_t)ctl.rays_extension;
+            progress->rays_shadow = (int64_t)ctl.rays_shadow;
+            progress->rays_reference = (int64_t)ctl.rays_reference;
+            progress->seconds = r->seconds;
+            progress->done = r->batches_done >= r->batches_total;
+        }
+    });
+}
+
+int b200pt_render_read(b200pt_render *r, float *rgb_sums, int64_t *spp_done)
+{
+    if (!r || !rgb_sums)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    return guarded([&] {
+        need_device(r->scene);
+        const size_t npix = (size_t)r->wf.npix;
+        std::vector<float4> tmp(npix);
+        CK(cudaMemcpyAsync(tmp.data(), r->film.accum, npix * sizeof(float4), cudaMemcpyDeviceToHost, r->scene->stream));
+        CK(cudaStreamSynchronize(r->scene->stream));
+        for (size_t i = 0; i < npix; i++) {
+            rgb_sums[3 * i + 0] = tmp[i].x;
+            rgb_sums[3 * i + 1] = tmp[i].y;
+            rgb_sums[3 * i + 2] = tmp[i].z;
+        }
+        if (spp_done)
+            *spp_done = r->spp_done;
+    });
+}
+
+int b200pt_render_read_stats(b200pt_render *r, float *clamped_sum, float *clamped_sumsq)
+{
+    if (!r || !clamped_sum || !clamped_sumsq)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    if (!r->film.csum)
+        return fail(B200PT_ERR_STATE, "render was started without config.stats_clamp");
+    return guarded([&] {
+        need_device(r->scene);
+        const size_t npix = (size_t)r->wf.npix;
+        std::vector<float4> a(npix), b(npix);
+        CK(cudaMemcpyAsync(a.data(), r->film.csum, npix * sizeof(float4), cudaMemcpyDeviceToHost, r->scene->stream));
+        CK(cudaMemcpyAsync(b.data(), r->film.csq, npix * sizeof(float4), cudaMemcpyDeviceToHost, r->scene->stream));
+        CK(cudaStreamSynchronize(r->scene->stream));
+        for (size_t i = 0; i < npix; i++) {
+            clamped_sum[3 * i + 0] = a[i].x;
+            clamped_sum[3 * i + 1] = a[i].y;
+            clamped_sum[3 * i + 2] = a[i].z;
+            clamped_sumsq[3 * i + 0] = b[i].x;
+            clamped_sumsq[3 * i + 1] = b[i].y;
+            clamped_sumsq[3 * i + 2] = b[i].z;
+        }
+    });
+}
+
+int b200pt_render_device_buffer(b200pt_render *r, void **d_accum, size_t *bytes)
+{
+    if (!r || !d_accum)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    *d_accum = r->film.accum;
+    if (bytes)
+        *bytes = (size_t)r->wf.npix * sizeof(float4);
+    return B200PT_OK;
+}
+
+int b200pt_render_write(b200pt_render *r, const float *rgba_sums, int64_t spp)
+{
+    if (!r || !rgba_sums)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    return guarded([&] {
+        need_device(r->scene);
+        CK(cudaMemcpyAsync(r->film.accum, rgba_sums, (size_t)r->wf.npix * sizeof(float4), cudaMemcpyHostToDevice,
+                           r->scene->stream));
+        CK(cudaStreamSynchronize(r->scene->stream));
+        r->spp_done = spp;
+    });
+}
+
+int b200pt_render_tonemap(b200pt_render *r, int64_t n_samples, uint8_t *rgb, float *max_luminance, float *avg_luminance)
+{
+    if (!r || n_samples <= 0)
+        return fail(B200PT_ERR_INVALID, "bad argument");
+    return guarded([&] {
+        need_device(r->scene);
+        cudaStream_t st = r->scene->stream;
+        const int npix = r->wf.npix;
+        // col /= float(samples) is a multiplication by float(1.0 / t) (vec3.h:181-189)
+        const float inv_n = (float)(1.0 / (float)n_samples);
+        pt::launch_luminance(r->film.accum, npix, inv_n, r->d_lum, st);
+        float lum[2];
+        CK(cudaMemcpyAsync(lum, r->d_lum, sizeof(lum), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        // renderer.h:37: col *= 16 + exposure
+        pt::launch_tonemap(r->film.accum, r->cfg.width, r->cfg.height, inv_n, 16 + r->cfg.exposure, lum[0], r->d_rgb, st);
+        CK(cudaGetLastError());
+        if (rgb)
+            CK(cudaMemcpyAsync(rgb, r->d_rgb, (size_t)npix * 3, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (max_luminance)
+            *max_luminance = lum[0];
+        if (avg_luminance) // helpers.h:167: total / (total_pixels * n_samples) (sic: divided by n twice)
+            *avg_luminance = lum[1] / ((float)npix * (float)n_samples);
+    });
+}
+
+int b200pt_render_write_ppm(b200pt_render *r, int64_t n_samples, const char *path)
+{
+    if (!r || !path)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    std::vector<uint8_t> rgb((size_t)r->wf.npix * 3);
+    int rc = b200pt_render_tonemap(r, n_samples, rgb.data(), nullptr, nullptr);
+    if (rc)
+        return rc;
+    std::ofstream f(path, std::ios::binary);
+    if (!f.good())
+        return fail(B200PT_ERR_INVALID, std::string("cannot open ") + path);
+    f << "P6\n" << r->cfg.width << " " << r->cfg.height << "\n255\n";
+    f.write((const char *)rgb.data(), (std::streamsize)rgb.size());
+    return f.good() ? B200PT_OK : fail(B200PT_ERR_INVALID, std::string("write failed: ") + path);
+}
+
+void b200pt_render_destroy(b200pt_render *r) { delete r; }
+
+} // extern "C"

@@ -1,0 +1,514 @@
+// kernels.cu -- the sm_100a kernels of the wavefront path tracer.
+//
+//   k_raygen      Tiled::compute's jitter + camera::get_ray (renderer.h:648-650, camera.h:38-47)
+//   k_extend      World::hit for every live path (world.h:17-20) + sort by material kind into shade queues
+//   k_shade       the vertex logic of NEEIterative::color / RecursivePT::color, one launch per material kind
+//   k_nee         light_samples shadow rays per vertex with light-pdf / BSDF-pdf MIS (integrator.h:221-265)
+//   k_accumulate  framebuffer[j][i] += de_nan(col) (renderer.h:670-682)
+//   k_luminance / k_tonemap   calculate_luminance + output_to_file (helpers.h:146-168, renderer.h:24-55)
+//   k_trace_batch the parity entry point (b200pt_trace_batch)
+//
+// Nothing here is a dense contraction, so tensor cores are not involved; the kernels are bound by fp32
+// intersection math, divergence and the L2/HBM traffic of the path state.
+#include "wavefront.cuh"
+
+namespace pt {
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+
+__device__ __forceinline__ V3 xyz(float4 a) { return v3(a.x, a.y, a.z); }
+__device__ __forceinline__ float4 f4(V3 a, float w) { return make_float4(a.x, a.y, a.z, w); }
+
+// Block-wide queue reservation: every thread passes a bit mask of the NQ queues it appends to.  Ranks come from
+// warp ballots, warp totals are prefix-summed in shared memory and ONE atomicAdd per (block, queue) reserves the
+// range.  Must be called by all threads of the block.
+template <int NQ>
+__device__ __forceinline__ void block_reserve(unsigned mask, int32_t *const (&counter)[NQ], int (&pos)[NQ])
+{
+    __shared__ int s_cnt[NQ][kWarps];
+    __shared__ int s_base[NQ];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    int rank[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; q++) {
+        unsigned b = __ballot_sync(0xffffffffu, (mask >> q) & 1u);
+        rank[q] = __popc(b & lt);
+        if (lane == 0)
+            s_cnt[q][warp] = __popc(b);
+    }
+    __syncthreads();
+    if (threadIdx.x < NQ) {
+        int total = 0;
+#pragma unroll
+        for (int w = 0; w < kWarps; w++) {
+            int c = s_cnt[threadIdx.x][w];
+            s_cnt[threadIdx.x][w] = total;
+            total += c;
+        }
+        s_base[threadIdx.x] = total ? atomicAdd(counter[threadIdx.x], total) : 0;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < NQ; q++)
+        pos[q] = s_base[q] + s_cnt[q][warp] + rank[q];
+    __syncthreads();
+}
+
+__device__ __forceinline__ RngKey make_key(const RenderParams &rp, const Wavefront &wf, int slot, long long sample_base)
+{
+    RngKey k;
+    k.seed_lo = rp.seed_lo;
+    k.seed_hi = rp.seed_hi;
+    int s_local = slot / wf.npix;
+    k.pixel = (uint32_t)(slot - s_local * wf.npix);
+    k.sample = (uint32_t)(sample_base + s_local);
+    return k;
+}
+
+__device__ __forceinline__ int shade_kind_of(int mat_kind)
+{
+    switch (mat_kind) {
+    case B200PT_MAT_DIELECTRIC: return SK_DIELECTRIC;
+    case B200PT_MAT_DIFFUSE_LIGHT: return SK_LIGHT;
+    case B200PT_MAT_ISOTROPIC: return SK_ISOTROPIC;
+    default: return SK_DIFFUSE; // lambertian and metal share one lobe (material.h:27-112)
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(kThreads) k_raygen(PtSceneView s, RenderParams rp, Wavefront wf)
+{
+    const long long sample_base = wf.ctl->sample_base;
+    const int n = wf.ctl->nsamp * wf.npix;
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        wf.counters[CNT_EXT] = n; // bounce 0 extends every slot (identity queue)
+    for (int slot = blockIdx.x * kThreads + threadIdx.x; slot < n; slot += gridDim.x * kThreads) {
+        RngKey key = make_key(rp, wf, slot, sample_base);
+        F4 r = rng4(key, stage_word(0, RNG_CAMERA, 0), 0);
+        int j = key.pixel / rp.width, i = key.pixel - j * rp.width; // row 0 = image bottom
+        float u = (float)(i + (double)r.x) / (float)rp.width;      // renderer.h:648-649
+        float v = (float)(j + (double)r.y) / (float)rp.height;
+        V3 o, d;
+        camera_ray(s.cam, u, v, r.z, r.w, o, d);
+        wf.ray_o[slot] = f4(o, -1.f); // last_bsdf_pdf = -1 (integrator.h:183)
+        wf.ray_d[slot] = f4(d, 0.f);
+        wf.beta[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+        wf.att[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+        wf.sum[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_extend(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
+{
+    const long long sample_base = wf.ctl->sample_base;
+    int32_t *row = wf.counters + bounce * CNT_ROW;
+    const int n = row[CNT_EXT];
+    const int32_t *q_in = bounce == 0 ? nullptr : wf.q_ext[bounce & 1];
+    int32_t *const kind_counter[SK_COUNT] = {row + CNT_KIND0, row + CNT_KIND0 + 1, row + CNT_KIND0 + 2,
+                                             row + CNT_KIND0 + 3, row + CNT_KIND0 + 4};
+    for (int base = blockIdx.x * kThreads; base < n; base += gridDim.x * kThreads) {
+        const int i = base + threadIdx.x;
+        unsigned mask = 0;
+        int slot = 0;
+        if (i < n) {
+            slot = q_in ? q_in[i] : i;
+            float4 ro = wf.ray_o[slot], rd = wf.ray_d[slot];
+            MediumRng mr;
+            mr.key = make_key(rp, wf, slot, sample_base);
+            mr.stage = stage_word(bounce, RNG_EXT_MEDIUM, 0);
+            mr.xi = -1.f;
+            Hit h;
+            int kind = SK_MISS;
+            if (trace_closest<false>(s, xyz(ro), xyz(rd), 0.001f, PT_FLT_MAX, mr, h, nullptr)) {
+                wf.hit_p[slot] = f4(h.p, __int_as_float(h.inst));
+                wf.hit_n[slot] = f4(h.n, h.t);
+                kind = shade_kind_of(s.mats[meta_material(s.inst[h.inst].meta)].kind);
+            }
+            mask = 1u << kind;
+        }
+        int pos[SK_COUNT];
+        block_reserve<SK_COUNT>(mask, kind_counter, pos);
+        if (mask) {
+            int kind = __ffs(mask) - 1;
+            wf.q_kind[kind][pos[kind]] = slot;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_shade(PtSceneView s, RenderParams rp, Wavefront wf, int bounce, int kind)
+{
+    const long long sample_base = wf.ctl->sample_base;
+    int32_t *row = wf.counters + bounce * CNT_ROW;
+    const int n = row[CNT_KIND0 + kind];
+    const int32_t *q_in = wf.q_kind[kind];
+    int32_t *q_next = wf.q_ext[(bounce + 1) & 1];
+    int32_t *const counter[2] = {row + CNT_NEE, row + CNT_ROW + CNT_EXT};
+    for (int base = blockIdx.x * kThreads; base < n; base += gridDim.x * kThreads) {
+        const int i = base + threadIdx.x;
+        unsigned mask = 0;
+        int slot = 0;
+        if (i < n) {
+            slot = q_in[i];
+            float4 ro = wf.ray_o[slot], rd = wf.ray_d[slot], bt = wf.beta[slot];
+            float4 acc = wf.sum[slot];
+            if (kind == SK_MISS) {
+                V3 add = shade_miss(s, xyz(rd), xyz(bt));
+                wf.sum[slot] = make_float4(acc.x + add.x, acc.y + add.y, acc.z + add.z, 0.f);
+            } else {
+                float4 hp = wf.hit_p[slot], hn = wf.hit_n[slot];
+                PathVertexIn in;
+                in.o = xyz(ro);
+                in.d = xyz(rd);
+                in.beta = xyz(bt);
+                in.last_bsdf_pdf = ro.w;
+                // only a light leaves `attenuation` as the previous vertex set it (material.h:187-191)
+                in.attenuation = kind == SK_LIGHT ? xyz(wf.att[slot]) : v3(0.f, 0.f, 0.f);
+                Hit rec;
+                rec.inst = __float_as_int(hp.w);
+                rec.p = xyz(hp);
+                rec.n = xyz(hn);
+                rec.t = hn.w;
+                rec.u = rec.v = 0.f;
+                RngKey key = make_key(rp, wf, slot, sample_base);
+                F4 rnd = rng4(key, stage_word(bounce, RNG_SHADE, 0), 0);
+                PathVertexOut out;
+                if (rp.integrator == B200PT_INTEGRATOR_INEEPT)
+                    shade_hit_ineept(s, rp, in, rec, rnd, out);
+                else
+                    shade_hit_rpt(s, rp, in, rec, bounce, rnd, out);
+                if (out.add.x != 0.f || out.add.y != 0.f || out.add.z != 0.f)
+                    wf.sum[slot] = make_float4(acc.x + out.add.x, acc.y + out.add.y, acc.z + out.add.z, 0.f);
+                if (out.want_nee) {
+                    wf.nee_w[slot] = f4(out.W, __int_as_float(out.mat_kind));
+                    mask |= 1u;
+                }
+                if (out.cont) {
+                    wf.ray_o[slot] = f4(out.o, out.last_bsdf_pdf);
+                    wf.ray_d[slot] = f4(out.d, 0.f);
+                    wf.beta[slot] = f4(out.beta, 0.f);
+                    wf.att[slot] = f4(out.attenuation, 0.f);
+                    mask |= 2u;
+                }
+            }
+        }
+        if (kind == SK_MISS)
+            continue; // uniform: a miss never appends
+        int pos[2];
+        block_reserve<2>(mask, counter, pos);
+        if (mask & 1u)
+            wf.q_nee[pos[0]] = slot;
+        if (mask & 2u)
+            q_next[pos[1]] = slot;
+    }
+}
+
+// One thread per (vertex, light sample).  With light_samples a power of two <= 32 the samples of one vertex sit in
+// adjacent lanes: same origin, nearly the same target -> coherent traversal, and the sum is a fixed-order shuffle
+// reduction; otherwise float atomics.
+__global__ void __launch_bounds__(kThreads) k_nee(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
+{
+    const long long sample_base = wf.ctl->sample_base;
+    const int L = rp.light_samples;
+    const long long n = (long long)wf.counters[bounce * CNT_ROW + CNT_NEE] * L;
+    const bool pow2 = (L & (L - 1)) == 0 && L <= 32;
+    const float inv_L_div = (float)L;
+    for (long long base = (long long)blockIdx.x * kThreads; base < n; base += (long long)gridDim.x * kThreads) {
+        const long long e = base + threadIdx.x;
+        V3 c = v3(0.f, 0.f, 0.f);
+        int slot = -1;
+        if (e < n) {
+            int q = (int)(e / L), k = (int)(e - (long long)q * L);
+            slot = wf.q_nee[q];
+            float4 hp = wf.hit_p[slot], hn = wf.hit_n[slot], w = wf.nee_w[slot];
+            RngKey key = make_key(rp, wf, slot, sample_base);
+            c = nee_sample<false>(s, rp, key, bounce, k, xyz(hp), xyz(hn), __float_as_int(w.w), xyz(w), nullptr);
+        }
+        if (pow2) {
+            // lanes [g*L, (g+1)*L) hold one vertex (kThreads and 32 are multiples of L)
+            for (int off = 1; off < L; off <<= 1) {
+                c.x += __shfl_xor_sync(0xffffffffu, c.x, off);
+                c.y += __shfl_xor_sync(0xffffffffu, c.y, off);
+                c.z += __shfl_xor_sync(0xffffffffu, c.z, off);
+            }
+            if (slot >= 0 && (threadIdx.x & (L - 1)) == 0 && (c.x != 0.f || c.y != 0.f || c.z != 0.f)) {
+                float4 acc = wf.sum[slot];
+                wf.sum[slot] =
+                    make_float4(acc.x + c.x / inv_L_div, acc.y + c.y / inv_L_div, acc.z + c.z / inv_L_div, 0.f);
+            }
+        } else if (slot >= 0) {
+            float *dst = reinterpret_cast<float *>(wf.sum + slot);
+            if (c.x != 0.f)
+                atomicAdd(dst + 0, c.x / inv_L_div);
+            if (c.y != 0.f)
+                atomicAdd(dst + 1, c.y / inv_L_div);
+            if (c.z != 0.f)
+                atomicAdd(dst + 2, c.z / inv_L_div);
+        }
+    }
+}
+
+// framebuffer[j][i] += de_nan(col): one thread per pixel walks the samples of the batch in order, so the film is
+// bit-reproducible.  Thread 0 of the LAST block to finish tallies the counters and advances the batch control.
+__global__ void __launch_bounds__(kThreads) k_accumulate(RenderParams rp, Wavefront wf, Film film, int n_rows)
+{
+    const int nsamp = wf.ctl->nsamp;
+    const int pix = blockIdx.x * kThreads + threadIdx.x;
+    if (pix < wf.npix) {
+        float4 acc = film.accum[pix];
+        float4 cs = make_float4(0.f, 0.f, 0.f, 0.f), cq = make_float4(0.f, 0.f, 0.f, 0.f);
+        const bool stats = film.csum != nullptr;
+        if (stats) {
+            cs = film.csum[pix];
+            cq = film.csq[pix];
+        }
+        for (int k = 0; k < nsamp; k++) {
+            float4 v = wf.sum[(size_t)k * wf.npix + pix];
+            float x = is_nan(v.x) ? 0.f : v.x, y = is_nan(v.y) ? 0.f : v.y, z = is_nan(v.z) ? 0.f : v.z; // de_nan
+            acc.x += x;
+            acc.y += y;
+            acc.z += z;
+            if (stats) {
+                float cx = fminf(x, film.clamp), cy = fminf(y, film.clamp), cz = fminf(z, film.clamp);
+                cs.x += cx;
+                cs.y += cy;
+                cs.z += cz;
+                cq.x += cx * cx;
+                cq.y += cy * cy;
+                cq.z += cz * cz;
+            }
+        }
+        film.accum[pix] = acc;
+        if (stats) {
+            film.csum[pix] = cs;
+            film.csq[pix] = cq;
+        }
+    }
+}
+
+__global__ void k_tally(RenderParams rp, Wavefront wf, int n_rows)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0)
+        return;
+    BatchCtl *c = wf.ctl;
+    unsigned long long ext = 0, shadow = 0, ref = 0;
+    for (int b = 0; b < n_rows; b++) {
+        const int32_t *row = wf.counters + b * CNT_ROW;
+        unsigned long long n_ext = (unsigned long long)row[CNT_EXT];
+        unsigned long long hits = n_ext - (unsigned long long)row[CNT_KIND0 + SK_MISS];
+        ext += n_ext;
+        if (rp.integrator == B200PT_INTEGRATOR_INEEPT) {
+            shadow += (unsigned long long)row[CNT_NEE] * (unsigned long long)rp.light_samples;
+            ref += n_ext + hits * (unsigned long long)rp.light_samples; // integrator.h:192,247
+        } else if (b > 0) {
+            ref += n_ext; // one count per scatter (integrator.h:45)
+        }
+    }
+    c->rays_extension += ext;
+    c->rays_shadow += shadow;
+    c->rays_reference += ref;
+    c->samples_done += (unsigned long long)c->nsamp * (unsigned long long)wf.npix;
+    c->sample_base += c->nsamp;
+    int next = c->remaining < c->batch_samples ? c->remaining : c->batch_samples;
+    c->remaining -= next;
+    c->nsamp = next;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kThreads) k_trace_batch(PtSceneView s, const float *__restrict__ rays, size_t n,
+                                                          const float *__restrict__ medium_xi,
+                                                          b200pt_hit *__restrict__ hits, unsigned long long *counts)
+{
+    unsigned long long boxes = 0, prims = 0, nhit = 0;
+    for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (size_t)gridDim.x * kThreads) {
+        const float4 *r4 = reinterpret_cast<const float4 *>(rays + i * 8);
+        float4 a = __ldg(r4), b = __ldg(r4 + 1);
+        MediumRng mr;
+        mr.key.seed_lo = 0;
+        mr.key.seed_hi = 0;
+        mr.key.pixel = (uint32_t)(i & 0xffffffffull);
+        mr.key.sample = (uint32_t)(i >> 32);
+        mr.stage = stage_word(0, RNG_BATCH_MEDIUM, 0);
+        mr.xi = medium_xi ? medium_xi[i] : -1.f;
+        Hit h;
+        TraceCounters tc;
+        tc.boxes = tc.prims = 0;
+        bool ok = trace_closest<COUNT>(s, v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), b.z, b.w, mr, h, &tc);
+        if (COUNT) {
+            boxes += tc.boxes;
+            prims += tc.prims;
+            nhit += ok ? 1 : 0;
+        }
+        if (hits) {
+            b200pt_hit o;
+            o.instance = ok ? h.inst : -1;
+            o.t = ok ? h.t : 0.f;
+            o.p[0] = ok ? h.p.x : 0.f, o.p[1] = ok ? h.p.y : 0.f, o.p[2] = ok ? h.p.z : 0.f;
+            o.n[0] = ok ? h.n.x : 0.f, o.n[1] = ok ? h.n.y : 0.f, o.n[2] = ok ? h.n.z : 0.f;
+            o.u = ok ? h.u : 0.f;
+            o.v = ok ? h.v : 0.f;
+            hits[i] = o;
+        }
+    }
+    if (COUNT) {
+        for (int off = 16; off > 0; off >>= 1) {
+            boxes += __shfl_down_sync(0xffffffffu, boxes, off);
+            prims += __shfl_down_sync(0xffffffffu, prims, off);
+            nhit += __shfl_down_sync(0xffffffffu, nhit, off);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(counts + 0, boxes);
+            atomicAdd(counts + 1, prims);
+            atomicAdd(counts + 2, nhit);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+
+// calculate_luminance (helpers.h:146-168): max and total over pixels of |de_nan(sum) / n|
+__global__ void __launch_bounds__(kThreads) k_luminance(const float4 *__restrict__ accum, int npix, float inv_n,
+                                                        float *max_total)
+{
+    float mx = 0.f, tot = 0.f;
+    for (int i = blockIdx.x * kThreads + threadIdx.x; i < npix; i += gridDim.x * kThreads) {
+        float4 v = accum[i];
+        V3 c = v3(is_nan(v.x) ? 0.f : v.x, is_nan(v.y) ? 0.f : v.y, is_nan(v.z) ? 0.f : v.z) * inv_n;
+        float f = length(c);
+        tot += f;
+        mx = fmaxf(mx, f);
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        mx = fmaxf(mx, __shfl_down_sync(0xffffffffu, mx, off));
+        tot += __shfl_down_sync(0xffffffffu, tot, off);
+    }
+    __shared__ float s_mx[kWarps], s_tot[kWarps];
+    if ((threadIdx.x & 31) == 0) {
+        s_mx[threadIdx.x >> 5] = mx;
+        s_tot[threadIdx.x >> 5] = tot;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < kWarps; w++) {
+            mx = fmaxf(mx, s_mx[w]);
+            tot += s_tot[w];
+        }
+        // lengths are >= 0: their float order equals the order of their bit patterns
+        atomicMax(reinterpret_cast<int *>(max_total), __float_as_int(mx));
+        atomicAdd(max_total + 1, tot);
+    }
+}
+
+__device__ __forceinline__ float uncharted2(float x)
+{
+    // tonemap.h:4-15
+    const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f;
+    return ((x * (A * x + C * B) + D * E) / (x * (A * x + B) + D * F)) - E / F;
+}
+
+__device__ __forceinline__ float to_srgb(float c)
+{
+    // helpers.h:78-88
+    if (c < 0.0031308f)
+        return 323 * c / 25;
+    return (211 * powf(c, 5.0f / 12) - 11) / 200;
+}
+
+__device__ __forceinline__ float clamp01(float x) { return x > 1.f ? 1.f : (x < 0.f ? 0.f : x); }
+
+// output_to_file (renderer.h:24-55): rows are written top (j = H-1) first
+__global__ void __launch_bounds__(kThreads) k_tonemap(const float4 *__restrict__ accum, int width, int height,
+                                                      float inv_n, float exposure_mul, float max_lum,
+                                                      uint8_t *__restrict__ rgb)
+{
+    const int npix = width * height;
+    const float white = uncharted2(max_lum);
+    for (int o = blockIdx.x * kThreads + threadIdx.x; o < npix; o += gridDim.x * kThreads) {
+        int row = o / width, i = o - row * width;
+        int j = height - 1 - row;
+        float4 v = accum[j * width + i];
+        float c[3] = {v.x, v.y, v.z};
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            float x = c[k] * inv_n;
+            x *= exposure_mul;
+            x = clamp01(uncharted2(x) / white);
+            x = 255 * to_srgb(x);
+            rgb[(size_t)o * 3 + k] = (uint8_t)(int)x;
+        }
+    }
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------------------------------
+
+void launch_raygen(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, const LaunchCfg &lc, cudaStream_t st)
+{
+    k_raygen<<<lc.blocks, kThreads, 0, st>>>(s, rp, wf);
+}
+
+void launch_extend(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, const LaunchCfg &lc,
+                   cudaStream_t st)
+{
+    k_extend<<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+}
+
+void launch_shade(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, int kind,
+                  const LaunchCfg &lc, cudaStream_t st)
+{
+    k_shade<<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce, kind);
+}
+
+void launch_nee(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, const LaunchCfg &lc,
+                cudaStream_t st)
+{
+    k_nee<<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+}
+
+void launch_accumulate(const RenderParams &rp, const Wavefront &wf, const Film &film, int n_rows, cudaStream_t st)
+{
+    int blocks = (wf.npix + kThreads - 1) / kThreads;
+    k_accumulate<<<blocks, kThreads, 0, st>>>(rp, wf, film, n_rows);
+    k_tally<<<1, 32, 0, st>>>(rp, wf, n_rows);
+}
+
+void launch_trace_batch(const PtSceneView &s, const float *rays, size_t n, const float *medium_xi, b200pt_hit *hits,
+                        unsigned long long *counts, cudaStream_t st)
+{
+    if (n == 0)
+        return;
+    size_t want = (n + kThreads - 1) / kThreads;
+    int blocks = (int)(want < (size_t)(148 * 16) ? want : (size_t)(148 * 16));
+    if (counts)
+        k_trace_batch<true><<<blocks, kThreads, 0, st>>>(s, rays, n, medium_xi, hits, counts);
+    else
+        k_trace_batch<false><<<blocks, kThreads, 0, st>>>(s, rays, n, medium_xi, hits, nullptr);
+}
+
+void launch_luminance(const float4 *accum, int npix, float inv_n, float *max_total, cudaStream_t st)
+{
+    cudaMemsetAsync(max_total, 0, 2 * sizeof(float), st);
+    int blocks = (npix + kThreads - 1) / kThreads;
+    if (blocks > 148 * 8)
+        blocks = 148 * 8;
+    k_luminance<<<blocks, kThreads, 0, st>>>(accum, npix, inv_n, max_total);
+}
+
+void launch_tonemap(const float4 *accum, int width, int height, float inv_n, float exposure_mul, float max_lum,
+                    uint8_t *rgb, cudaStream_t st)
+{
+    int npix = width * height;
+    int blocks = (npix + kThreads - 1) / kThreads;
+    if (blocks > 148 * 8)
+        blocks = 148 * 8;
+    k_tonemap<<<blocks, kThreads, 0, st>>>(accum, width, height, inv_n, exposure_mul, max_lum, rgb);
+}
+
+} // namespace pt

@@ -1,0 +1,356 @@
+// pt_intersect.h -- closest-hit queries: primitive tests, the instance wrapper, the constant medium and the
+// ordered stack traversal of the flat BVH.  Formula order follows the reference so that t / normal agree to
+// fp32 rounding:
+//   sphere::hit           primitive.h:64-95        rect::hit      primitive.h:186-225
+//   box (6 rects, list)   primitive.h:233-246, hittable_list.h:21-38
+//   constant_medium::hit  volume.h:29-93           instance::hit  primitive.h:298-312
+//   aabb::hit             aabb.h:34-53             bvh_node::hit  bvh.h:31-69 (same closest hit, fewer visits)
+#pragma once
+#include "pt_rng.h"
+#include "pt_scene.h"
+
+namespace pt {
+
+struct PrimHit {
+    float t;
+    V3 n; // local-space normal
+    float u, v;
+};
+
+struct Hit {
+    int32_t inst; // -1: miss
+    float t;
+    V3 p, n;
+    float u, v;
+};
+
+PT_HD V3 shuffle(V3 v, int plane)
+{
+    // primitive.h:104-121
+    if (plane == B200PT_PLANE_XY)
+        return v3(v.x, v.z, v.y);
+    if (plane == B200PT_PLANE_YZ)
+        return v3(v.y, v.x, v.z);
+    return v;
+}
+
+PT_HD bool hit_sphere(V3 center, float radius, V3 o, V3 d, float t_min, float t_max, PrimHit &h)
+{
+    V3 oc = o - center;
+    float a = dot(d, d);
+    float b = dot(oc, d);
+    float c = dot(oc, oc) - radius * radius;
+    float discriminant = b * b - a * c;
+    if (discriminant > 0) {
+        float sq = sqrtf(discriminant);
+        float temp = (-b - sq) / a;
+        if (!(temp < t_max && temp > t_min)) {
+            temp = (-b + sq) / a;
+            if (!(temp < t_max && temp > t_min))
+                return false;
+        }
+        h.t = temp;
+        V3 p = o + temp * d;
+        h.n = (p - center) / radius;
+        h.u = 0.f; // left unset by the reference (Q11)
+        h.v = 0.f;
+        return true;
+    }
+    return false;
+}
+
+PT_HD bool hit_rect(int plane, bool flip, float x0, float z0, float x1, float z1, float y, V3 o, V3 d, float t0,
+                    float t1, PrimHit &h)
+{
+    V3 to = shuffle(o, plane);
+    V3 td = shuffle(d, plane);
+    float t = (y - to.y) / td.y;
+    if (t < t0 || t > t1) // NB a NaN t passes, as in the reference
+        return false;
+    float xh = to.x + t * td.x;
+    float zh = to.z + t * td.z;
+    if (xh < x0 || xh > x1 || zh < z0 || zh > z1)
+        return false;
+    h.u = (xh - x0) / (x1 - x0);
+    h.v = (zh - x0) / (z1 - z0); // sic: x0 (primitive.h:207)
+    h.t = t;
+    V3 n = shuffle(v3(0.f, flip ? -1.f : 1.f, 0.f), plane);
+    if (dot(d, n) > 0) // two_sided is hard-wired true (primitive.h:181,214-222)
+        n = -n;
+    h.n = n;
+    return true;
+}
+
+PT_HD bool hit_box(const float *p, V3 o, V3 d, float t_min, float t_max, PrimHit &h)
+{
+    // box::box builds sides in this order (primitive.h:233-240); hittable_list::hit keeps the last hit with
+    // t <= closest_so_far (inclusive upper bound in rect::hit).
+    bool any = false;
+    float closest = t_max;
+    PrimHit tmp;
+    if (hit_rect(B200PT_PLANE_XY, true, p[0], p[1], p[3], p[4], p[2], o, d, t_min, closest, tmp)) {
+        any = true;
+        closest = tmp.t;
+        h = tmp;
+    }
+    if (hit_rect(B200PT_PLANE_XY, false, p[0], p[1], p[3], p[4], p[5], o, d, t_min, closest, tmp)) {
+        any = true;
+        closest = tmp.t;
+        h = tmp;
+    }
+    if (hit_rect(B200PT_PLANE_YZ, true, p[1], p[2], p[4], p[5], p[0], o, d, t_min, closest, tmp)) {
+        any = true;
+        closest = tmp.t;
+        h = tmp;
+    }
+    if (hit_rect(B200PT_PLANE_YZ, false, p[1], p[2], p[4], p[5], p[3], o, d, t_min, closest, tmp)) {
+        any = true;
+        closest = tmp.t;
+        h = tmp;
+    }
+    if (hit_rect(B200PT_PLANE_XZ, true, p[0], p[2], p[3], p[5], p[1], o, d, t_min, closest, tmp)) {
+        any = true;
+        closest = tmp.t;
+        h = tmp;
+    }
+    if (hit_rect(B200PT_PLANE_XZ, false, p[0], p[2], p[3], p[5], p[4], o, d, t_min, closest, tmp)) {
+        any = true;
+        closest = tmp.t;
+        h = tmp;
+    }
+    return any;
+}
+
+// the bare primitive (sphere | rect | box) in its local frame
+PT_HD bool hit_prim(uint32_t meta, const float *p, V3 o, V3 d, float t_min, float t_max, PrimHit &h)
+{
+    int kind = meta_kind(meta);
+    if (kind == B200PT_PRIM_SPHERE)
+        return hit_sphere(v3(p[0], p[1], p[2]), p[3], o, d, t_min, t_max, h);
+    if (kind == B200PT_PRIM_RECT)
+        return hit_rect(meta_plane(meta), meta_flip(meta), p[0], p[1], p[2], p[3], p[4], o, d, t_min, t_max, h);
+    return hit_box(p, o, d, t_min, t_max, h);
+}
+
+// constant_medium::hit (volume.h:29-93).  xi = the uniform variate of volume.h:70.  xi2 >= 0: a second,
+// independent variate for a medium that the reference BVH holds twice (bvh.h:150-153; both copies are
+// intersected and the nearer event wins, which is the minimum of two free-flight draws).
+PT_HD bool hit_medium(uint32_t meta, const float *p, float density, V3 o, V3 d, float t_min, float t_max, float xi,
+                      float xi2, PrimHit &h)
+{
+    PrimHit rec1, rec2;
+    if (!hit_prim(meta, p, o, d, -PT_FLT_MAX, PT_FLT_MAX, rec1))
+        return false;
+    if (!hit_prim(meta, p, o, d, rec1.t + 0.0001f, PT_FLT_MAX, rec2))
+        return false;
+    float ta = rec1.t, tb = rec2.t;
+    if (ta < t_min)
+        ta = t_min;
+    if (tb > t_max)
+        tb = t_max;
+    if (ta >= tb)
+        return false;
+    if (ta < 0)
+        ta = 0;
+    float dlen = length(d);
+    float distance_inside_boundary = (tb - ta) * dlen;
+    float hit_distance = -(1.f / density) * logf(xi);
+    if (xi2 >= 0.f) {
+        float hd2 = -(1.f / density) * logf(xi2);
+        hit_distance = hd2 < hit_distance ? hd2 : hit_distance;
+    }
+    if (hit_distance < distance_inside_boundary) {
+        h.t = ta + hit_distance / dlen;
+        h.n = v3(1.f, 0.f, 0.f); // "arbitrary" (volume.h:86)
+        h.u = 0.f;
+        h.v = 0.f;
+        return true;
+    }
+    return false;
+}
+
+// Where a traversal gets the medium variates from.
+struct MediumRng {
+    RngKey key;
+    uint32_t stage; // stage word; index = medium slot
+    float xi;       // >= 0: explicit variate for every medium (b200pt_trace_batch); < 0: use the Philox stream
+};
+
+struct InstanceData { // one PtInstance in registers
+    float inv[12];
+    uint32_t meta;
+    float p[6];
+    float density;
+};
+
+PT_HD void load_instance(const PtInstance *table, int idx, InstanceData &I)
+{
+#if defined(__CUDA_ARCH__)
+    const float4 *q = reinterpret_cast<const float4 *>(table + idx);
+    float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3), e = __ldg(q + 4);
+    I.inv[0] = a.x, I.inv[1] = a.y, I.inv[2] = a.z, I.inv[3] = a.w;
+    I.inv[4] = b.x, I.inv[5] = b.y, I.inv[6] = b.z, I.inv[7] = b.w;
+    I.inv[8] = c.x, I.inv[9] = c.y, I.inv[10] = c.z, I.inv[11] = c.w;
+    I.meta = __float_as_uint(d.x);
+    I.p[0] = d.y, I.p[1] = d.z, I.p[2] = d.w;
+    I.p[3] = e.x, I.p[4] = e.y, I.p[5] = e.z;
+    I.density = e.w;
+#else
+    const PtInstance &s = table[idx];
+    for (int i = 0; i < 12; i++)
+        I.inv[i] = s.inv[i];
+    I.meta = s.meta;
+    for (int i = 0; i < 6; i++)
+        I.p[i] = s.p[i];
+    I.density = s.density;
+#endif
+}
+
+// instance::hit without the world-space epilogue: local ray, local hit record, t preserved (primitive.h:298-301).
+PT_HD bool hit_instance(const InstanceData &I, V3 o, V3 d, float t_min, float t_max, const MediumRng &mr, PrimHit &h)
+{
+    V3 lo = xform_point(I.inv, o);
+    V3 ld = xform_vector(I.inv, d);
+    if (!meta_medium(I.meta))
+        return hit_prim(I.meta, I.p, lo, ld, t_min, t_max, h);
+    float xi = mr.xi, xi2 = -1.f;
+    if (xi < 0.f) {
+        F4 r = rng4(mr.key, mr.stage, meta_medium_slot(I.meta));
+        xi = r.x;
+        if (meta_dup(I.meta))
+            xi2 = r.y;
+    }
+    return hit_medium(I.meta, I.p, I.density, lo, ld, t_min, t_max, xi, xi2, h);
+}
+
+// aabb::hit (aabb.h:34-53) against one child half; returns the entry parameter in t_entry.
+PT_HD bool hit_aabb(const float *lo, const float *hi, V3 o, V3 inv_d, float t_min, float t_max, float &t_entry)
+{
+    float t0 = (lo[0] - o.x) * inv_d.x, t1 = (hi[0] - o.x) * inv_d.x;
+    float tn = fminf(t0, t1), tf = fmaxf(t0, t1);
+    t_min = fmaxf(tn, t_min); // fmaxf/fminf drop NaNs like the reference's `t0 > tmin ? t0 : tmin`
+    t_max = fminf(tf, t_max);
+    t0 = (lo[1] - o.y) * inv_d.y, t1 = (hi[1] - o.y) * inv_d.y;
+    tn = fminf(t0, t1), tf = fmaxf(t0, t1);
+    t_min = fmaxf(tn, t_min);
+    t_max = fminf(tf, t_max);
+    t0 = (lo[2] - o.z) * inv_d.z, t1 = (hi[2] - o.z) * inv_d.z;
+    tn = fminf(t0, t1), tf = fmaxf(t0, t1);
+    t_min = fmaxf(tn, t_min);
+    t_max = fminf(tf, t_max);
+    t_entry = t_min;
+    return t_max > t_min;
+}
+
+struct TraceCounters {
+    uint32_t boxes, prims;
+};
+
+#define PT_STACK_DEPTH 48
+
+// World::hit (world.h:17-20): closest hit over the whole scene in [t_min, t_max].
+template <bool COUNT>
+PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_max, const MediumRng &mr, Hit &out,
+                         TraceCounters *counters)
+{
+    const V3 inv_d = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    float best_t = t_max;
+    int best_inst = -1;
+    PrimHit best;
+    best.t = 0.f;
+    best.n = v3(0.f, 0.f, 0.f);
+    best.u = best.v = 0.f;
+
+    int32_t stack_ref[PT_STACK_DEPTH];
+    float stack_t[PT_STACK_DEPTH];
+    int sp = 0;
+    int32_t cur = 0; // root node
+    bool have = true;
+    while (have) {
+        while (cur >= 0) {
+            const PtNode *node = s.nodes + cur;
+#if defined(__CUDA_ARCH__)
+            const float4 *q = reinterpret_cast<const float4 *>(node);
+            float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), e = __ldg(q + 3);
+            float lo0[3] = {a.x, a.y, a.z}, hi0[3] = {b.x, b.y, b.z}, lo1[3] = {c.x, c.y, c.z}, hi1[3] = {e.x, e.y, e.z};
+            int32_t ref0 = __float_as_int(a.w), ref1 = __float_as_int(c.w);
+#else
+            const float *lo0 = node->lo0, *hi0 = node->hi0, *lo1 = node->lo1, *hi1 = node->hi1;
+            int32_t ref0 = node->ref0, ref1 = node->ref1;
+#endif
+            float e0, e1;
+            bool h0 = hit_aabb(lo0, hi0, o, inv_d, t_min, best_t, e0);
+            bool h1 = hit_aabb(lo1, hi1, o, inv_d, t_min, best_t, e1);
+            if (COUNT)
+                counters->boxes += 2;
+            if (h0 && h1) {
+                int32_t near_ref = ref0, far_ref = ref1;
+                float far_t = e1;
+                if (e1 < e0) {
+                    near_ref = ref1;
+                    far_ref = ref0;
+                    far_t = e0;
+                }
+                if (sp < PT_STACK_DEPTH) {
+                    stack_ref[sp] = far_ref;
+                    stack_t[sp] = far_t;
+                    sp++;
+                }
+                cur = near_ref;
+            } else if (h0) {
+                cur = ref0;
+            } else if (h1) {
+                cur = ref1;
+            } else {
+                have = false;
+                break;
+            }
+        }
+        if (have) {
+            // leaf: one instance
+            int idx = ~cur;
+            InstanceData I;
+            load_instance(s.inst, idx, I);
+            PrimHit h;
+            if (COUNT)
+                counters->prims += 1;
+            if (hit_instance(I, o, d, t_min, best_t, mr, h)) {
+                // strict '<' like bvh_node::hit's `left_rec.t < right_rec.t` choice is immaterial: the range
+                // handed down is already clipped to best_t
+                best_t = h.t;
+                best = h;
+                best_inst = idx;
+            }
+        }
+        // pop
+        have = false;
+        while (sp > 0) {
+            sp--;
+            if (stack_t[sp] < best_t) {
+                cur = stack_ref[sp];
+                have = true;
+                break;
+            }
+        }
+    }
+    if (best_inst < 0) {
+        out.inst = -1;
+        return false;
+    }
+    // instance::hit epilogue (primitive.h:302-305): p and normal back to world space
+    InstanceData I;
+    load_instance(s.inst, best_inst, I);
+    V3 lo = xform_point(I.inv, o);
+    V3 ld = xform_vector(I.inv, d);
+    V3 pl = lo + best.t * ld;
+    const float *fwd = s.fwd[best_inst].m;
+    out.inst = best_inst;
+    out.t = best.t;
+    out.p = xform_point(fwd, pl);
+    out.n = unit_vector(xform_vector_transposed(I.inv, best.n));
+    out.u = best.u;
+    out.v = best.v;
+    return true;
+}
+
+} // namespace pt

@@ -1,0 +1,65 @@
+// pt_scene.h -- the device-resident scene: plain structs, 16-byte aligned, uploaded once.
+//
+//   PtNode      64 B  one BVH2 node = two 32-byte child halves {lo.xyz, ref | hi.xyz, pad}; a half is what a ray
+//                     tests (slab test) before descending, fetched as 2 x 128-bit loads.
+//   PtInstance  80 B  world->local 3x4 (48 B) + tagged-union primitive (32 B): meta word, 6 params, density.
+//   PtFwd       48 B  local->world 3x4, fetched only for the closest hit and for light sampling.
+//   b200pt_material / b200pt_texture (32 B each) are used as they come from the C ABI.
+#pragma once
+#include "../../../include/b200pt.h"
+#include "pt_math.h"
+
+namespace pt {
+
+struct alignas(16) PtNode {
+    float lo0[3];
+    int32_t ref0; // >= 0: inner node index; < 0: ~ref = instance index
+    float hi0[3];
+    int32_t pad0;
+    float lo1[3];
+    int32_t ref1;
+    float hi1[3];
+    int32_t pad1;
+};
+
+// meta: bits 0-1 prim kind | 2-3 rect plane | 4 rect flip | 5 medium | 6 bvh-dup | 7 light | 8-15 medium slot |
+//       16-31 material index
+struct alignas(16) PtInstance {
+    float inv[12];
+    uint32_t meta;
+    float p[6];
+    float density;
+};
+
+struct alignas(16) PtFwd {
+    float m[12];
+};
+
+PT_HD int meta_kind(uint32_t m) { return (int)(m & 3u); }
+PT_HD int meta_plane(uint32_t m) { return (int)((m >> 2) & 3u); }
+PT_HD bool meta_flip(uint32_t m) { return (m >> 4) & 1u; }
+PT_HD bool meta_medium(uint32_t m) { return (m >> 5) & 1u; }
+PT_HD bool meta_dup(uint32_t m) { return (m >> 6) & 1u; }
+PT_HD bool meta_light(uint32_t m) { return (m >> 7) & 1u; }
+PT_HD uint32_t meta_medium_slot(uint32_t m) { return (m >> 8) & 0xffu; }
+PT_HD int meta_material(uint32_t m) { return (int)(m >> 16); }
+
+struct PtCamera {
+    V3 origin, lower_left, horizontal, vertical, u, v;
+    float lens_radius;
+};
+
+struct PtSceneView {
+    const PtNode *nodes;
+    const PtInstance *inst;
+    const PtFwd *fwd;
+    const b200pt_material *mats;
+    const b200pt_texture *tex;
+    const int32_t *lights;
+    const float *perlin_ranvec; // 256 x 3
+    const int32_t *perlin_perm; // 3 x 256
+    int32_t n_nodes, n_inst, n_lights, background;
+    PtCamera cam;
+};
+
+} // namespace pt

@@ -1,0 +1,447 @@
+// pt_shade.h -- what happens at a path vertex: textures, material scatter/emission, BSDF sampling and pdfs,
+// light sampling and the next-event-estimation sample with its MIS weight.  One function per stage of the
+// reference's NEEIterative::color loop (integrator.h:176-339) and RecursivePT::color (integrator.h:29-72); the
+// quirks of the code at HEAD are kept on purpose and marked "sic".
+#pragma once
+#include "pt_intersect.h"
+
+namespace pt {
+
+struct RenderParams {
+    int32_t width, height;
+    int32_t integrator; // B200PT_INTEGRATOR_*
+    int32_t max_bounces, light_samples;
+    int32_t russian_roulette, only_direct;
+    float normal_offset;
+    uint32_t seed_lo, seed_hi;
+};
+
+// ---- textures (texture.h) ---------------------------------------------------------------------------------------
+
+PT_HD float perlin_noise(const PtSceneView &s, V3 p)
+{
+    // perlin::noise (texture.h:132-156) + perlin_interp (texture.h:111-130): the smoothstep is applied twice (sic)
+    float fx = floorf(p.x), fy = floorf(p.y), fz = floorf(p.z);
+    float u = p.x - fx, v = p.y - fy, w = p.z - fz;
+    u = u * u * (3 - 2 * u);
+    v = v * v * (3 - 2 * v);
+    w = w * w * (3 - 2 * w);
+    int i = (int)fx, j = (int)fy, k = (int)fz;
+    float uu = u * u * (3 - 2 * u);
+    float vv = v * v * (3 - 2 * v);
+    float ww = w * w * (3 - 2 * w);
+    float accum = 0;
+    for (int di = 0; di < 2; di++)
+        for (int dj = 0; dj < 2; dj++)
+            for (int dk = 0; dk < 2; dk++) {
+                int idx = s.perlin_perm[(i + di) & 255] ^ s.perlin_perm[256 + ((j + dj) & 255)] ^
+                          s.perlin_perm[512 + ((k + dk) & 255)];
+                V3 c = v3(s.perlin_ranvec[idx * 3], s.perlin_ranvec[idx * 3 + 1], s.perlin_ranvec[idx * 3 + 2]);
+                V3 weight_v = v3(u - di, v - dj, w - dk);
+                accum += (di * uu + (1 - di) * (1 - uu)) * (dj * vv + (1 - dj) * (1 - vv)) *
+                         (dk * ww + (1 - dk) * (1 - ww)) * dot(c, weight_v);
+            }
+    return accum;
+}
+
+// texture::value and texture::alpha in one walk (checker textures may nest, texture.h:46-68)
+PT_HD void tex_eval(const PtSceneView &s, int id, V3 p, V3 &value, float &alpha)
+{
+    for (int depth = 0; depth < 8; depth++) {
+        const b200pt_texture &t = s.tex[id];
+        if (t.kind == B200PT_TEX_CHECKER) {
+            float sines = sinf(t.scale * p.x) * sinf(t.scale * p.y) * sinf(t.scale * p.z);
+            id = sines > 0 ? t.odd : t.even;
+            continue;
+        }
+        if (t.kind == B200PT_TEX_PERLIN) {
+            float nz = perlin_noise(s, t.scale * p);
+            value = v3(nz, nz, nz); // vec3(1,1,1) * noise (texture.h:191); may be negative (sic)
+            alpha = 1.0f;
+            return;
+        }
+        value = v3(t.color[0], t.color[1], t.color[2]);
+        alpha = t.alpha;
+        return;
+    }
+    value = v3(0.f, 0.f, 0.f);
+    alpha = 1.f;
+}
+
+// ---- materials (material.h) -------------------------------------------------------------------------------------
+
+// material::emitted: only diffuse_light overrides it (material.h:209-228); isotropic's 3-argument `emitted`
+// does not override the 5-argument virtual (material.h:263-266), so media never emit.
+PT_HD V3 mat_emitted(const PtSceneView &s, const b200pt_material &m, V3 ray_dir, V3 n, V3 p)
+{
+    if (m.kind != B200PT_MAT_DIFFUSE_LIGHT)
+        return v3(0.f, 0.f, 0.f);
+    bool aligned = dot(n, ray_dir) > 0;
+    if (!aligned || m.two_sided) {
+        V3 value;
+        float alpha;
+        tex_eval(s, m.texture, p, value, alpha);
+        return (m.power * value) * alpha;
+    }
+    return v3(0.f, 0.f, 0.f);
+}
+
+// material::scatter: returns did_scatter; `attenuation` is left untouched by a light (material.h:187-191), so the
+// caller's value from the previous vertex survives (integrator.h:181,199).
+PT_HD bool mat_scatter(const PtSceneView &s, const b200pt_material &m, V3 ray_dir, V3 n, V3 p, V3 &attenuation)
+{
+    switch (m.kind) {
+    case B200PT_MAT_LAMBERTIAN: {
+        if (dot(ray_dir, n) < 0) {
+            V3 value;
+            float alpha;
+            tex_eval(s, m.texture, p, value, alpha);
+            attenuation = value / PT_PI_F;
+        } else {
+            attenuation = v3(0.f, 0.f, 0.f);
+        }
+        return true;
+    }
+    case B200PT_MAT_METAL: // a cosine lobe with constant albedo, no facing test (material.h:90-98) (sic)
+        attenuation = v3(m.color[0], m.color[1], m.color[2]) / PT_PI_F;
+        return true;
+    case B200PT_MAT_DIELECTRIC:
+        attenuation = v3(1.f, 1.f, 1.f);
+        return true;
+    case B200PT_MAT_ISOTROPIC: {
+        V3 value;
+        float alpha;
+        tex_eval(s, m.texture, p, value, alpha);
+        attenuation = value; // no 1/4pi (material.h:259) (sic)
+        return true;
+    }
+    default:
+        return false;
+    }
+}
+
+// material::value: the pdf the material's own sampler has for `direction`
+PT_HD float mat_value(int kind, V3 n, V3 direction)
+{
+    if (kind == B200PT_MAT_LAMBERTIAN || kind == B200PT_MAT_METAL) {
+        // cosine_pdf::value (pdf.h:18-28); uvw.w() = unit_vector(n)
+        float cosine = dot(unit_vector(direction), unit_vector(n));
+        return cosine > 0 ? cosine / PT_PI_F : 0.f;
+    }
+    if (kind == B200PT_MAT_ISOTROPIC)
+        return (float)(1 / (4 * 3.14159265358979323846)); // random_pdf::value (pdf.h:41-44)
+    return 0.f;                                          // void_pdf (pdf.h:71-74): dielectric, diffuse_light
+}
+
+PT_HD V3 random_in_unit_sphere(float r1, float r2, float r3)
+{
+    // random.h:17-24: a point INSIDE the ball (radius r3^(1/3)), y-up spherical coordinates
+    float u = r1 * 2 * PT_PI_F;
+    float v = acosf(2 * r2 - 1);
+    float w = powf(r3, 1.0f / 3.0f);
+    return v3(cosf(u) * sinf(v) * w, cosf(v) * w, sinf(u) * sinf(v) * w);
+}
+
+PT_HD V3 random_cosine_direction(float r1, float r2)
+{
+    // random.h:35-44
+    float z = sqrtf(1 - r2);
+    float phi = 2 * PT_PI_F * r1;
+    float sq = sqrtf(r2);
+    return v3(cosf(phi) * sq, sinf(phi) * sq, z);
+}
+
+PT_HD V3 reflect(V3 v, V3 n) { return v - 2 * dot(v, n) * n; }
+
+PT_HD bool refract(V3 v, V3 n, float ni_over_nt, V3 &refracted)
+{
+    // helpers.h:24-36
+    V3 uv = unit_vector(v);
+    float dt = dot(uv, n);
+    float discriminant = 1.0f - ni_over_nt * ni_over_nt * (1 - dt * dt);
+    if (discriminant > 0) {
+        refracted = ni_over_nt * (uv - n * dt) - n * sqrtf(discriminant);
+        return true;
+    }
+    return false;
+}
+
+PT_HD float schlick(float cosine, float ref_idx)
+{
+    float r0 = (1 - ref_idx) / (1 + ref_idx);
+    r0 = r0 * r0;
+    float c = 1 - cosine;
+    return r0 + (1 - r0) * (c * c * c * c * c);
+}
+
+// material::generate
+PT_HD V3 mat_generate(const b200pt_material &m, V3 ray_dir, V3 n, float r1, float r2, float r3)
+{
+    if (m.kind == B200PT_MAT_LAMBERTIAN || m.kind == B200PT_MAT_METAL) {
+        Onb uvw = onb_from_w(n);
+        return onb_local(uvw, random_cosine_direction(r1, r2));
+    }
+    if (m.kind == B200PT_MAT_DIELECTRIC) {
+        // material.h:125-167
+        V3 outward_normal;
+        V3 reflected = reflect(ray_dir, n);
+        float ni_over_nt, cosine, reflect_prob;
+        V3 refracted = v3(0.f, 0.f, 0.f);
+        float dlen = length(ray_dir);
+        if (dot(ray_dir, n) > 0) {
+            outward_normal = -n;
+            ni_over_nt = m.ior;
+            cosine = m.ior * dot(ray_dir, n) / dlen;
+        } else {
+            outward_normal = n;
+            ni_over_nt = 1.0f / m.ior;
+            cosine = -dot(ray_dir, n) / dlen;
+        }
+        if (refract(ray_dir, outward_normal, ni_over_nt, refracted))
+            reflect_prob = schlick(cosine, m.ior);
+        else
+            reflect_prob = 1.0f;
+        return r1 < reflect_prob ? reflected : refracted;
+    }
+    // isotropic: random_pdf::generate; diffuse_light: void_pdf::generate (pdf.h:45-48,75-78)
+    return random_in_unit_sphere(r1, r2, r3);
+}
+
+// ---- lights (hittable::random / pdf_value through the instance wrapper, primitive.h:319-342) ------------------
+
+PT_HD V3 light_random(const InstanceData &I, const float *fwd, V3 o, float r1, float r2)
+{
+    V3 lo = xform_point(I.inv, o);
+    V3 dl;
+    int kind = meta_kind(I.meta);
+    if (meta_medium(I.meta) || kind == B200PT_PRIM_BOX) {
+        dl = v3(1.f, 0.f, 0.f); // hittable::random default (hittable.h:28): box and constant_medium do not override
+    } else if (kind == B200PT_PRIM_RECT) {
+        // rect::random (primitive.h:172-178)
+        V3 pt = shuffle(v3(I.p[0] + r1 * (I.p[2] - I.p[0]), I.p[4], I.p[1] + r2 * (I.p[3] - I.p[1])), meta_plane(I.meta));
+        dl = pt - lo;
+    } else {
+        // sphere::random (primitive.h:51-58) + random_to_sphere (random.h:46-55)
+        V3 center = v3(I.p[0], I.p[1], I.p[2]);
+        float radius = I.p[3];
+        V3 direction = center - lo;
+        float distance_squared = squared_length(direction);
+        Onb uvw = onb_from_w(direction);
+        float z = 1 + r2 * (sqrtf(1 - radius * radius / distance_squared) - 1);
+        float phi = 2 * PT_PI_F * r1;
+        float sq = sqrtf(1 - z * z);
+        dl = onb_local(uvw, v3(cosf(phi) * sq, sinf(phi) * sq, z));
+    }
+    return xform_vector(fwd, dl);
+}
+
+PT_HD float light_pdf_value(const InstanceData &I, V3 o, V3 v)
+{
+    int kind = meta_kind(I.meta);
+    if (meta_medium(I.meta) || kind == B200PT_PRIM_BOX)
+        return 0.f; // hittable::pdf_value default (hittable.h:27)
+    V3 lo = xform_point(I.inv, o);
+    V3 lv = xform_vector(I.inv, v);
+    PrimHit rec;
+    if (kind == B200PT_PRIM_RECT) {
+        // rect::pdf_value (primitive.h:156-171): all lengths are LOCAL-space lengths (sic)
+        if (hit_rect(meta_plane(I.meta), meta_flip(I.meta), I.p[0], I.p[1], I.p[2], I.p[3], I.p[4], lo, lv, 0.001f,
+                     PT_FLT_MAX, rec)) {
+            float area = (I.p[2] - I.p[0]) * (I.p[3] - I.p[1]);
+            float vlen = length(lv);
+            float d = rec.t * vlen;
+            float distance_squared = d * d;
+            float cosine = fabsf(dot(lv, rec.n) / vlen);
+            return distance_squared / (cosine * area);
+        }
+        return 0.f;
+    }
+    // sphere::pdf_value (primitive.h:37-50)
+    V3 center = v3(I.p[0], I.p[1], I.p[2]);
+    float radius = I.p[3];
+    if (hit_sphere(center, radius, lo, lv, 0.001f, PT_FLT_MAX, rec)) {
+        float cos_theta_max = sqrtf(1 - radius * radius / squared_length(center - lo));
+        float solid_angle = 2 * PT_PI_F * (1 - cos_theta_max);
+        return 1 / solid_angle;
+    }
+    return 0.f;
+}
+
+PT_HD float power_heuristic(float f, float g)
+{
+    // helpers.h:138-144 with nf = ng = 1, pow = 2
+    float f2 = f * f;
+    return f2 / (f2 + g * g);
+}
+
+// ---- one next-event-estimation sample (integrator.h:221-265) --------------------------------------------------
+// W = attenuation * beta at the vertex.  Returns the contribution of light sample k (before the division by
+// light_samples); `traced` tells whether a shadow ray was cast.
+template <bool COUNT>
+PT_HD V3 nee_sample(const PtSceneView &s, const RenderParams &rp, const RngKey &key, int bounce, int k, V3 p, V3 n,
+                    int mat_kind, V3 W, TraceCounters *counters)
+{
+    F4 r = rng4(key, stage_word(bounce, RNG_NEE, k), 0);
+    int li = (int)(r.x * s.n_lights); // World::get_random_light (world.h:31-35)
+    if (li >= s.n_lights)
+        li = s.n_lights - 1;
+    const int light_inst = s.lights[li];
+    const float pick_pdf = (float)s.n_lights; // (sic) integrator.h:224
+    InstanceData L;
+    load_instance(s.inst, light_inst, L);
+    V3 dir = light_random(L, s.fwd[light_inst].m, p, r.y, r.z);
+    float cos_l = dot(unit_vector(dir), unit_vector(n));
+    float light_pdf_l = light_pdf_value(L, p, dir);
+    float scatter_pdf_l = mat_value(mat_kind, n, dir);
+    float weight_l = power_heuristic(light_pdf_l, scatter_pdf_l);
+
+    MediumRng mr;
+    mr.key = key;
+    mr.stage = stage_word(bounce, RNG_NEE_MEDIUM, k);
+    mr.xi = -1.f;
+    Hit lrec;
+    // the shadow ray starts at the un-offset hit point; t is in units of |dir| (integrator.h:235,246) (sic)
+    if (!trace_closest<COUNT>(s, p, dir, 0.001f, PT_FLT_MAX, mr, lrec, counters))
+        return v3(0.f, 0.f, 0.f);
+    // whatever is hit first contributes its emission -- `true ||` (integrator.h:250) (sic)
+    const b200pt_material &lm = s.mats[meta_material(s.inst[lrec.inst].meta)];
+    V3 light_emission = mat_emitted(s, lm, dir, lrec.n, lrec.p);
+    float dropoff = fmaxf(cos_l, 0.0f);
+    V3 c = W * weight_l;
+    c = c / light_pdf_l;
+    c = c * dropoff;
+    c = c * light_emission;
+    c = c / pick_pdf;
+    if (is_nan(c))
+        return v3(0.f, 0.f, 0.f);
+    return c;
+}
+
+// ---- the vertex: emission, NEE request, scattering, Russian roulette, throughput (integrator.h:193-323) ------
+
+struct PathVertexIn {
+    V3 o, d;        // the ray that arrived
+    V3 beta;        // throughput
+    V3 attenuation; // value left by the previous vertex (integrator.h:181)
+    float last_bsdf_pdf;
+};
+
+struct PathVertexOut {
+    V3 add;         // radiance to add to the sample now
+    bool want_nee;  // run light_samples NEE samples with W, at (p, n, mat_kind)
+    V3 W;
+    int mat_kind;
+    bool cont;      // path continues with the fields below
+    V3 o, d, beta, attenuation;
+    float last_bsdf_pdf;
+};
+
+PT_HD void shade_hit_ineept(const PtSceneView &s, const RenderParams &rp, const PathVertexIn &in, const Hit &rec, F4 rnd,
+                            PathVertexOut &out)
+{
+    const uint32_t meta = s.inst[rec.inst].meta;
+    const b200pt_material &m = s.mats[meta_material(meta)];
+    out.add = v3(0.f, 0.f, 0.f);
+    out.cont = false;
+    out.mat_kind = m.kind;
+    V3 attenuation = in.attenuation;
+    bool did_scatter = mat_scatter(s, m, in.d, rec.n, rec.p, attenuation);
+    float cos_i = fabsf(dot(unit_vector(in.d), unit_vector(rec.n))); // cosine of the INCOMING ray (sic)
+    V3 hit_emission = mat_emitted(s, m, in.d, rec.n, rec.p);
+    if (squared_length(hit_emission) > 0.000001f) {
+        if (in.last_bsdf_pdf <= 0) {
+            out.add += in.beta * hit_emission;
+        } else {
+            // hittable_pdf(rec.primitive, r.origin()).value(rec.p): the hit POINT is passed as direction (sic, Q3)
+            InstanceData I;
+            load_instance(s.inst, rec.inst, I);
+            float weight = power_heuristic(in.last_bsdf_pdf, light_pdf_value(I, in.o, rec.p));
+            out.add += (in.beta * hit_emission) * weight;
+        }
+    }
+    // NEE is skipped when it cannot contribute (integrator.h:248); the rays the reference would still cast are
+    // accounted for by the caller
+    out.want_nee = length(attenuation) > 0.0001f && s.n_lights > 0;
+    out.W = attenuation * in.beta;
+
+    if (did_scatter) {
+        V3 dir = mat_generate(m, in.d, rec.n, rnd.x, rnd.y, rnd.z);
+        float scatter_pdf_s = mat_value(m.kind, rec.n, dir);
+        V3 beta = in.beta;
+        float pmax = fmaxf(beta.x, fmaxf(beta.y, beta.z));
+        if (rp.russian_roulette && pmax <= 1 && 0.001f < pmax) {
+            if (rnd.w > pmax)
+                return;
+            beta = beta * (1 / pmax);
+        }
+        if (rp.only_direct)
+            return;
+        if (scatter_pdf_s < 0.0000001f)
+            return;
+        beta = beta * (attenuation * cos_i / scatter_pdf_s); // (sic, Q4)
+        // Q12: a path whose throughput is exactly zero can add nothing any more; the reference keeps tracing it
+        if (beta.x == 0.f && beta.y == 0.f && beta.z == 0.f)
+            return;
+        out.cont = true;
+        out.o = rec.p + rp.normal_offset * rec.n;
+        out.d = dir;
+        out.beta = beta;
+        out.attenuation = attenuation;
+        out.last_bsdf_pdf = scatter_pdf_s;
+    } else {
+        out.add += in.beta * hit_emission; // emission counted a second time (sic, Q2)
+    }
+}
+
+// RecursivePT::color unrolled: radiance = sum over vertices of (product of attenuations) * emitted
+// (integrator.h:29-72).  depth = index of this vertex (0 = first hit).
+PT_HD void shade_hit_rpt(const PtSceneView &s, const RenderParams &rp, const PathVertexIn &in, const Hit &rec, int depth,
+                         F4 rnd, PathVertexOut &out)
+{
+    const uint32_t meta = s.inst[rec.inst].meta;
+    const b200pt_material &m = s.mats[meta_material(meta)];
+    out.want_nee = false;
+    out.cont = false;
+    out.mat_kind = m.kind;
+    out.W = v3(0.f, 0.f, 0.f);
+    V3 emitted = mat_emitted(s, m, in.d, rec.n, rec.p);
+    out.add = in.beta * emitted;
+    V3 attenuation = in.attenuation;
+    if (depth < rp.max_bounces && mat_scatter(s, m, in.d, rec.n, rec.p, attenuation)) {
+        V3 beta = in.beta * attenuation;
+        if (beta.x == 0.f && beta.y == 0.f && beta.z == 0.f)
+            return;
+        out.cont = true;
+        out.o = rec.p; // no normal offset in this integrator (integrator.h:44)
+        out.d = mat_generate(m, in.d, rec.n, rnd.x, rnd.y, rnd.z);
+        out.beta = beta;
+        out.attenuation = attenuation;
+        out.last_bsdf_pdf = -1.f;
+    }
+}
+
+// miss: background lookup (integrator.h:63-69,325-335).  u,v only matter for image textures; p = unit direction.
+PT_HD V3 shade_miss(const PtSceneView &s, V3 d, V3 beta)
+{
+    V3 value;
+    float alpha;
+    tex_eval(s, s.background, unit_vector(d), value, alpha);
+    return beta * value;
+}
+
+// camera::get_ray (camera.h:38-47) for film coordinates (s, t); rd = lens sample in the unit disk
+PT_HD void camera_ray(const PtCamera &c, float sx, float ty, float r1, float r2, V3 &o, V3 &d)
+{
+    V3 offset = v3(0.f, 0.f, 0.f);
+    if (c.lens_radius > 0.f) {
+        // random_in_unit_disk (random.h:26-33)
+        float u = r1 * 2 * PT_PI_F;
+        float v = sqrtf(r2);
+        V3 rd = c.lens_radius * v3(cosf(u) * v, sinf(u) * v, 0.f);
+        offset = c.u * rd.x + c.v * rd.y;
+    }
+    o = c.origin + offset;
+    d = c.lower_left + sx * c.horizontal + ty * c.vertical - c.origin - offset;
+}
+
+} // namespace pt

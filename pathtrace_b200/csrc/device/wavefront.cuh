@@ -1,0 +1,80 @@
+// wavefront.cuh -- device-side layout of one wavefront batch and the launch interface of the kernels.
+//
+// A batch renders `nsamp` samples of every pixel: slot = s_local * npix + pixel.  All per-path state lives in
+// float4 SoA arrays indexed by slot (one 128-bit access per field); the kernels of one bounce are connected by
+// queues of slot indices, compacted with warp ballots and a block prefix sum in shared memory:
+//
+//   raygen -> [ extend -> shade{miss,diffuse,dielectric,light,isotropic} -> nee ] x bounces -> accumulate
+//
+// Queue sizes live in `counters` on the device (row = bounce), so the host never waits between kernels.
+#pragma once
+#include "pt_shade.h"
+
+#include <cuda_runtime.h>
+
+namespace pt {
+
+enum ShadeKind { SK_MISS = 0, SK_DIFFUSE = 1, SK_DIELECTRIC = 2, SK_LIGHT = 3, SK_ISOTROPIC = 4, SK_COUNT = 5 };
+
+// counters row layout (int32 each)
+enum { CNT_EXT = 0, CNT_KIND0 = 1 /* ..5 */, CNT_NEE = 6, CNT_ROW = 8 };
+
+struct BatchCtl {           // device-resident, advanced by the tally kernel at the end of every batch
+    int64_t sample_base;    // first global sample index of the current batch
+    int32_t nsamp;          // samples per pixel in the current batch
+    int32_t remaining;      // samples per pixel still to render after the current batch
+    int32_t batch_samples;  // nominal samples per batch
+    int32_t pad;
+    // running totals
+    unsigned long long rays_extension, rays_shadow, rays_reference, samples_done;
+};
+
+struct Wavefront {
+    float4 *ray_o; // o.xyz, last_bsdf_pdf
+    float4 *ray_d; // d.xyz, -
+    float4 *beta;  // beta.xyz, -
+    float4 *att;   // attenuation.xyz of the previous vertex, -
+    float4 *hit_p; // p.xyz, instance (int bits; -1 = miss)
+    float4 *hit_n; // n.xyz, t
+    float4 *nee_w; // W.xyz = attenuation*beta, material kind (int bits)
+    float4 *sum;   // radiance of the sample so far
+    int32_t *q_ext[2];
+    int32_t *q_kind[SK_COUNT];
+    int32_t *q_nee;
+    int32_t *counters; // (max_bounces + 2) rows of CNT_ROW
+    BatchCtl *ctl;
+    int32_t npix;
+    int32_t capacity; // slots
+};
+
+struct Film {
+    float4 *accum; // per pixel radiance sums (row 0 = image bottom), .w unused
+    float4 *csum;  // parity statistics: sum of clamped samples (or null)
+    float4 *csq;   //                    sum of squares of clamped samples
+    float clamp;
+};
+
+struct LaunchCfg {
+    int blocks;  // grid size for the queue-driven kernels (persistent, grid-stride)
+    int threads; // 256
+};
+
+void launch_raygen(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, const LaunchCfg &lc, cudaStream_t st);
+void launch_extend(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, const LaunchCfg &lc,
+                   cudaStream_t st);
+void launch_shade(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, int kind,
+                  const LaunchCfg &lc, cudaStream_t st);
+void launch_nee(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, const LaunchCfg &lc,
+                cudaStream_t st);
+void launch_accumulate(const RenderParams &rp, const Wavefront &wf, const Film &film, int n_rows, cudaStream_t st);
+
+// closest-hit batch (b200pt_trace_batch): rays n x 8 floats, hits n x b200pt_hit
+void launch_trace_batch(const PtSceneView &s, const float *rays, size_t n, const float *medium_xi, b200pt_hit *hits,
+                        unsigned long long *counts, cudaStream_t st);
+
+// film: luminance reduce (max, total of |sum/n|) and tonemap to bytes (top row first)
+void launch_luminance(const float4 *accum, int npix, float inv_n, float *max_total /* [2] */, cudaStream_t st);
+void launch_tonemap(const float4 *accum, int width, int height, float inv_n, float exposure_mul, float max_lum,
+                    uint8_t *rgb, cudaStream_t st);
+
+} // namespace pt

@@ -1,0 +1,53 @@
+// flat_scene.h -- host-side flat scene (the output of the scene compiler, the input of the uploader).
+#pragma once
+#include "../../../include/b200pt.h"
+#include "json.h"
+
+#include <string>
+#include <vector>
+
+namespace b200pt {
+
+struct Aabb {
+    float lo[3], hi[3];
+};
+
+struct FlatScene {
+    std::vector<b200pt_instance> instances;
+    std::vector<b200pt_material> materials;
+    std::vector<b200pt_texture> textures;
+    std::vector<int32_t> lights;
+    int32_t background = 0;
+    b200pt_camera camera{};
+    std::vector<float> perlin_ranvec;  // 256*3 (always filled: cheap)
+    std::vector<int32_t> perlin_perm;  // 3*256
+    std::vector<std::string> warnings; // parser warnings the reference prints to stdout
+
+    b200pt_scene_desc desc() const;
+    static FlatScene from_desc(const b200pt_scene_desc &d);
+};
+
+// build_scene (scene_parser.h:241-595) + setup_camera (main.cpp:86-104).  Throws std::runtime_error.
+FlatScene compile_scene(const Json &scene, int film_width, int film_height);
+
+// camera::camera (camera.h:9-36) in the reference's float arithmetic.
+b200pt_camera make_camera(const float lookfrom[3], const float lookat[3], float vfov_deg, float aspect, float aperture,
+                          float focus_dist);
+
+// transform3(scale, rotate, translate) (transform3.h:17-25): T * Rx * Ry * Rz * S, angles in units of pi, composed
+// through unit quaternions exactly as Eigen 3.2.10 does for AngleAxisf products, in float.
+void make_transform(const float scale[3], const float rotate[3], const float translate[3], float out[12]);
+
+// Inverse of a 3x4 affine (computed in double, rounded once).  Returns false when singular.
+bool invert_affine(const float m[12], float out[12]);
+
+// instance::instance bbox (primitive.h:266-297): the primitive's own box, 8 corners through the transform.
+Aabb instance_bounds(const b200pt_instance &inst);
+
+// The reference draws its Perlin tables (texture.h:76-110,180-183) and its BVH split axes (bvh.h:135) from
+// one default-seeded std::mt19937 (random.h:9-15).  This replays that stream: fills the tables, then walks the
+// same recursive median-split build over the instance list to find which instances end up alone in an n==1
+// leaf (bvh.h:150-153), where the reference intersects them twice.
+void replay_reference_rng(FlatScene &scene);
+
+} // namespace b200pt

@@ -1,0 +1,86 @@
+#include "scene_pack.h"
+
+#include <cstring>
+#include <stdexcept>
+#include <string>
+
+namespace b200pt {
+
+static pt::V3 to_v3(const float *p) { return pt::v3(p[0], p[1], p[2]); }
+
+PackedScene pack_scene(const FlatScene &f)
+{
+    PackedScene out;
+    const int n = (int)f.instances.size();
+    if (n <= 0)
+        throw std::runtime_error("scene has no instances");
+    if (f.materials.size() > 65535)
+        throw std::runtime_error("too many materials (16-bit material index)");
+    out.inst.resize(n);
+    out.fwd.resize(n);
+    std::vector<Aabb> boxes(n);
+    int media = 0;
+    for (int i = 0; i < n; i++) {
+        const b200pt_instance &src = f.instances[i];
+        pt::PtInstance &dst = out.inst[i];
+        // transform3::inverse() is re-derived by the reference on every call (transform3.h:51-54); here once
+        if (!invert_affine(src.fwd, dst.inv))
+            throw std::runtime_error("instance " + std::to_string(i) + " has a singular transform");
+        memcpy(out.fwd[i].m, src.fwd, sizeof(src.fwd));
+        uint32_t meta = (uint32_t)(src.prim_kind & 3) | ((uint32_t)(src.plane & 3) << 2);
+        if (src.flags & B200PT_INST_RECT_FLIP)
+            meta |= 1u << 4;
+        if (src.flags & B200PT_INST_MEDIUM) {
+            if (media >= 256)
+                throw std::runtime_error("more than 256 media in one scene");
+            meta |= 1u << 5;
+            meta |= (uint32_t)media << 8;
+            media++;
+        }
+        if (src.flags & B200PT_INST_BVH_DUP)
+            meta |= 1u << 6;
+        if (src.light_index >= 0)
+            meta |= 1u << 7;
+        meta |= (uint32_t)src.material << 16;
+        dst.meta = meta;
+        memcpy(dst.p, src.params, sizeof(dst.p));
+        dst.density = src.density;
+        boxes[i] = instance_bounds(src);
+    }
+    out.n_media = media;
+    out.bvh = build_bvh(boxes);
+    out.perlin_ranvec = f.perlin_ranvec;
+    out.perlin_perm = f.perlin_perm;
+    if (out.perlin_ranvec.size() != 768)
+        out.perlin_ranvec.assign(768, 0.f);
+    if (out.perlin_perm.size() != 768)
+        out.perlin_perm.assign(768, 0);
+    return out;
+}
+
+pt::PtSceneView PackedScene::host_view(const FlatScene &f) const
+{
+    pt::PtSceneView v{};
+    v.nodes = bvh.nodes.data();
+    v.inst = inst.data();
+    v.fwd = fwd.data();
+    v.mats = f.materials.data();
+    v.tex = f.textures.data();
+    v.lights = f.lights.data();
+    v.perlin_ranvec = perlin_ranvec.data();
+    v.perlin_perm = perlin_perm.data();
+    v.n_nodes = (int)bvh.nodes.size();
+    v.n_inst = (int)inst.size();
+    v.n_lights = (int)f.lights.size();
+    v.background = f.background;
+    v.cam.origin = to_v3(f.camera.origin);
+    v.cam.lower_left = to_v3(f.camera.lower_left);
+    v.cam.horizontal = to_v3(f.camera.horizontal);
+    v.cam.vertical = to_v3(f.camera.vertical);
+    v.cam.u = to_v3(f.camera.u);
+    v.cam.v = to_v3(f.camera.v);
+    v.cam.lens_radius = f.camera.lens_radius;
+    return v;
+}
+
+} // namespace b200pt

@@ -1,0 +1,24 @@
+// scene_pack.h -- FlatScene -> the arrays the kernels read (PtInstance / PtFwd / PtNode), still in host memory.
+#pragma once
+#include "../device/pt_scene.h"
+#include "bvh_build.h"
+#include "flat_scene.h"
+
+#include <vector>
+
+namespace b200pt {
+
+struct PackedScene {
+    std::vector<pt::PtInstance> inst;
+    std::vector<pt::PtFwd> fwd;
+    BuiltBvh bvh;
+    std::vector<float> perlin_ranvec;  // 768
+    std::vector<int32_t> perlin_perm;  // 768
+    int n_media = 0;
+    // a view whose pointers refer to THIS object's host vectors and to `flat`'s material/texture/light arrays
+    pt::PtSceneView host_view(const FlatScene &flat) const;
+};
+
+PackedScene pack_scene(const FlatScene &flat);
+
+} // namespace b200pt
