@@ -223,24 +223,31 @@ PT_HD bool hit_instance(const InstanceData &I, V3 o, V3 d, float t_min, float t_
     return hit_medium(I.meta, I.p, I.density, lo, ld, t_min, t_max, xi, xi2, h);
 }
 
-// aabb::hit (aabb.h:34-53) against one child half; returns the entry parameter in t_entry.
-PT_HD bool hit_aabb(const float *lo, const float *hi, V3 o, V3 inv_d, float t_min, float t_max, float &t_entry)
+// aabb::hit (aabb.h:34-53) of one child half, used as a culling test against [t_min, t_limit] (inclusive).
+// (b - o) * (1/d) is the reference's own expression; a primitive's t comes from a true division, so the two can
+// differ by an ulp: the caller passes t_limit = closest t so far widened by a few ulps, which can only let a ray
+// visit a subtree it did not need, never skip one whose primitive it hits -- including a primitive at EXACTLY
+// the current closest t, which must still be offered to the tie rule in trace_closest.
+PT_HD bool hit_aabb(const float *lo, const float *hi, V3 o, V3 inv_d, float t_min, float t_limit, float &t_entry)
 {
     float t0 = (lo[0] - o.x) * inv_d.x, t1 = (hi[0] - o.x) * inv_d.x;
     float tn = fminf(t0, t1), tf = fmaxf(t0, t1);
     t_min = fmaxf(tn, t_min); // fmaxf/fminf drop NaNs like the reference's `t0 > tmin ? t0 : tmin`
-    t_max = fminf(tf, t_max);
+    t_limit = fminf(tf, t_limit);
     t0 = (lo[1] - o.y) * inv_d.y, t1 = (hi[1] - o.y) * inv_d.y;
     tn = fminf(t0, t1), tf = fmaxf(t0, t1);
     t_min = fmaxf(tn, t_min);
-    t_max = fminf(tf, t_max);
+    t_limit = fminf(tf, t_limit);
     t0 = (lo[2] - o.z) * inv_d.z, t1 = (hi[2] - o.z) * inv_d.z;
     tn = fminf(t0, t1), tf = fmaxf(t0, t1);
     t_min = fmaxf(tn, t_min);
-    t_max = fminf(tf, t_max);
+    t_limit = fminf(tf, t_limit);
     t_entry = t_min;
-    return t_max > t_min;
+    return t_limit >= t_min;
 }
+
+// closest t so far, widened by ~3 ulps for the culling tests
+PT_HD float cull_limit(float best_t) { return best_t + fabsf(best_t) * 4e-7f; }
 
 struct TraceCounters {
     uint32_t boxes, prims;
@@ -279,8 +286,9 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
             int32_t ref0 = node->ref0, ref1 = node->ref1;
 #endif
             float e0, e1;
-            bool h0 = hit_aabb(lo0, hi0, o, inv_d, t_min, best_t, e0);
-            bool h1 = hit_aabb(lo1, hi1, o, inv_d, t_min, best_t, e1);
+            const float lim = cull_limit(best_t);
+            bool h0 = hit_aabb(lo0, hi0, o, inv_d, t_min, lim, e0);
+            bool h1 = hit_aabb(lo1, hi1, o, inv_d, t_min, lim, e1);
             if (COUNT)
                 counters->boxes += 2;
             if (h0 && h1) {
@@ -314,9 +322,12 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
             PrimHit h;
             if (COUNT)
                 counters->prims += 1;
-            if (hit_instance(I, o, d, t_min, best_t, mr, h)) {
-                // strict '<' like bvh_node::hit's `left_rec.t < right_rec.t` choice is immaterial: the range
-                // handed down is already clipped to best_t
+            // Every primitive test is inclusive at its upper bound or never ties (rect: `t > t1` rejects,
+            // primitive.h:196; sphere: strict), so a surface at exactly best_t is reported again.  The reference
+            // hands the unshrunk t_max to both children and keeps the RIGHT record unless left.t < right.t
+            // (bvh.h:39-48): among equal t the right-most leaf of ITS tree wins.  The instance table is stored in
+            // that leaf order (scene_compile.cpp), hence: a tie goes to the higher index.
+            if (hit_instance(I, o, d, t_min, best_t, mr, h) && (h.t < best_t || idx > best_inst)) {
                 best_t = h.t;
                 best = h;
                 best_inst = idx;
@@ -324,9 +335,10 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
         }
         // pop
         have = false;
+        const float lim = cull_limit(best_t);
         while (sp > 0) {
             sp--;
-            if (stack_t[sp] < best_t) {
+            if (stack_t[sp] <= lim) {
                 cur = stack_ref[sp];
                 have = true;
                 break;
@@ -347,7 +359,7 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
     out.inst = best_inst;
     out.t = best.t;
     out.p = xform_point(fwd, pl);
-    out.n = unit_vector(xform_vector_transposed(I.inv, best.n));
+    out.n = eigen_normalized(xform_vector_transposed(I.inv, best.n));
     out.u = best.u;
     out.v = best.v;
     return true;

@@ -47,6 +47,13 @@ PT_HD V3 cross(V3 a, V3 b) { return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * 
 PT_HD float length(V3 a) { return sqrtf(a.x * a.x + a.y * a.y + a.z * a.z); }
 PT_HD float squared_length(V3 a) { return a.x * a.x + a.y * a.y + a.z * a.z; }
 PT_HD V3 unit_vector(V3 a) { return a / length(a); } // vec3.h:196-199
+// Eigen 3.2.10 Vector3f::normalized(): v / sqrt(x*x + (y*y + z*z)) -- its 3-element sum splits 1 + 2
+// (Core/Redux.h redux_novec_unroller).  Used where the reference normalises through Eigen (transform3.h:60-63).
+PT_HD V3 eigen_normalized(V3 a)
+{
+    float yz = a.y * a.y + a.z * a.z;
+    return a / sqrtf(a.x * a.x + yz);
+}
 PT_HD bool is_nan(float x) { return !(x == x); }
 PT_HD bool is_nan(V3 a) { return is_nan(a.x) || is_nan(a.y) || is_nan(a.z); }
 PT_HD float get(V3 a, int i) { return i == 0 ? a.x : (i == 1 ? a.y : a.z); }

@@ -38,7 +38,8 @@ b200pt_camera make_camera(const float lookfrom[3], const float lookat[3], float 
 // through unit quaternions exactly as Eigen 3.2.10 does for AngleAxisf products, in float.
 void make_transform(const float scale[3], const float rotate[3], const float translate[3], float out[12]);
 
-// Inverse of a 3x4 affine (computed in double, rounded once).  Returns false when singular.
+// Inverse of a 3x4 affine exactly as Eigen 3.2.10 computes Affine3f::inverse() in float (the reference calls it on
+// every hit, transform3.h:51-54).  Returns false when singular.
 bool invert_affine(const float m[12], float out[12]);
 
 // instance::instance bbox (primitive.h:266-297): the primitive's own box, 8 corners through the transform.
@@ -47,7 +48,9 @@ Aabb instance_bounds(const b200pt_instance &inst);
 // The reference draws its Perlin tables (texture.h:76-110,180-183) and its BVH split axes (bvh.h:135) from
 // one default-seeded std::mt19937 (random.h:9-15).  This replays that stream: fills the tables, then walks the
 // same recursive median-split build over the instance list to find which instances end up alone in an n==1
-// leaf (bvh.h:150-153), where the reference intersects them twice.
+// leaf (bvh.h:150-153), where the reference intersects them twice, and REORDERS `instances` into the left-to-right
+// leaf order of that tree (lights[] is re-indexed), so that the reference's tie rule for coincident surfaces
+// (bvh.h:57-60: the right child wins) becomes "the higher instance index wins".
 void replay_reference_rng(FlatScene &scene);
 
 } // namespace b200pt

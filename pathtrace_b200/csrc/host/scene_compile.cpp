@@ -369,34 +369,43 @@ void make_transform(const float scale[3], const float rotate[3], const float tra
     }
 }
 
+// Eigen 3.2.10's Affine3f::inverse() in the reference's own float arithmetic (Transform.h:1158-1185 ->
+// LU/Inverse.h:120-159): 3x3 inverse by cofactors (det = c0*m00 + (c1*m10 + c2*m20), every entry = cofactor *
+// (1/det)), translation = -(inv * t) summed left to right.  The reference re-derives this on every hit
+// (transform3.h:51-54); bit-equal matrices are what keeps near-surface rays (|o - surface| << |o|) in agreement.
+// Compiled without FMA contraction (x86-64 baseline), like the reference.
 bool invert_affine(const float m[12], float out[12])
 {
-    double a[3][3], t[3];
-    for (int r = 0; r < 3; r++) {
-        for (int c = 0; c < 3; c++)
-            a[r][c] = m[r * 4 + c];
-        t[r] = m[r * 4 + 3];
-    }
-    double c00 = a[1][1] * a[2][2] - a[1][2] * a[2][1];
-    double c01 = a[1][2] * a[2][0] - a[1][0] * a[2][2];
-    double c02 = a[1][0] * a[2][1] - a[1][1] * a[2][0];
-    double det = a[0][0] * c00 + a[0][1] * c01 + a[0][2] * c02;
-    if (det == 0.0 || !std::isfinite(det))
+    auto M = [&](int r, int c) -> float { return m[r * 4 + c]; };
+    auto cof = [&](int i, int j) -> float {
+        const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+        volatile float a = M(i1, j1) * M(i2, j2);
+        volatile float b = M(i1, j2) * M(i2, j1);
+        return a - b;
+    };
+    const float c0 = cof(0, 0), c1 = cof(1, 0), c2 = cof(2, 0);
+    volatile float p0 = c0 * M(0, 0), p1 = c1 * M(1, 0), p2 = c2 * M(2, 0);
+    volatile float s12 = p1 + p2;
+    const float det = p0 + s12;
+    if (det == 0.0f || !std::isfinite(det))
         return false;
-    double inv[3][3];
-    inv[0][0] = c00 / det;
-    inv[0][1] = (a[0][2] * a[2][1] - a[0][1] * a[2][2]) / det;
-    inv[0][2] = (a[0][1] * a[1][2] - a[0][2] * a[1][1]) / det;
-    inv[1][0] = c01 / det;
-    inv[1][1] = (a[0][0] * a[2][2] - a[0][2] * a[2][0]) / det;
-    inv[1][2] = (a[0][2] * a[1][0] - a[0][0] * a[1][2]) / det;
-    inv[2][0] = c02 / det;
-    inv[2][1] = (a[0][1] * a[2][0] - a[0][0] * a[2][1]) / det;
-    inv[2][2] = (a[0][0] * a[1][1] - a[0][1] * a[1][0]) / det;
+    const float invdet = 1.0f / det;
+    float inv[3][3];
+    inv[0][0] = c0 * invdet;
+    inv[0][1] = c1 * invdet;
+    inv[0][2] = c2 * invdet;
+    inv[1][0] = cof(0, 1) * invdet;
+    inv[1][1] = cof(1, 1) * invdet;
+    inv[1][2] = cof(2, 1) * invdet;
+    inv[2][0] = cof(0, 2) * invdet;
+    inv[2][1] = cof(1, 2) * invdet;
+    inv[2][2] = cof(2, 2) * invdet;
     for (int r = 0; r < 3; r++) {
         for (int c = 0; c < 3; c++)
-            out[r * 4 + c] = (float)inv[r][c];
-        out[r * 4 + 3] = (float)(-(inv[r][0] * t[0] + inv[r][1] * t[1] + inv[r][2] * t[2]));
+            out[r * 4 + c] = inv[r][c];
+        volatile float q0 = inv[r][0] * m[3], q1 = inv[r][1] * m[7], q2 = inv[r][2] * m[11];
+        volatile float q01 = q0 + q1;
+        out[r * 4 + 3] = -(q01 + q2);
     }
     return true;
 }
@@ -573,12 +582,23 @@ void replay_reference_rng(FlatScene &scene)
     }
     if (n > 0)
         ref_bvh_walk(rng, boxes, order.data(), n, dup);
+    // `order` now lists the instances as the leaves of the reference tree, left to right.  bvh_node::hit keeps the
+    // RIGHT child's record when both children report the same t (bvh.h:57-60), so among exactly coincident
+    // surfaces (a box standing on the floor) the right-most leaf wins.  The instance table is stored in that
+    // order, which turns the rule into "the higher instance index wins a tie" (trace_closest).
+    std::vector<b200pt_instance> sorted(n);
+    std::vector<int32_t> new_index(n);
     for (int i = 0; i < n; i++) {
-        if (dup[i])
-            scene.instances[i].flags |= B200PT_INST_BVH_DUP;
+        sorted[i] = scene.instances[order[i]];
+        if (dup[order[i]])
+            sorted[i].flags |= B200PT_INST_BVH_DUP;
         else
-            scene.instances[i].flags &= ~B200PT_INST_BVH_DUP;
+            sorted[i].flags &= ~B200PT_INST_BVH_DUP;
+        new_index[order[i]] = i;
     }
+    scene.instances.swap(sorted);
+    for (int32_t &l : scene.lights)
+        l = new_index[l];
 }
 
 FlatScene compile_scene(const Json &scene, int film_width, int film_height)
