@@ -136,6 +136,9 @@ typedef struct b200pt_config {
     int32_t batch_samples;  /* samples per pixel per wavefront batch; 0 = auto */
     float stats_clamp;      /* >0: also accumulate per-pixel sum / sum of squares of the per-sample
                                radiance clamped at this value (parity statistics) */
+    int32_t profile;        /* measurement aid: 1 = bracket every kernel launch with CUDA events on the render stream
+                               (per-kernel device time), 2 = run the traversal kernels with work counters on
+                               (BVH boxes / primitives tested); see b200pt_render_profile.  0 in production. */
 } b200pt_config;
 
 typedef struct b200pt_scene b200pt_scene;
@@ -222,6 +225,23 @@ int b200pt_render_tonemap(b200pt_render *render, int64_t n_samples, uint8_t *rgb
                           float *avg_luminance);
 /* Writes "P6\nW H\n255\n" + payload (renderer.h:26-53). */
 int b200pt_render_write_ppm(b200pt_render *render, int64_t n_samples, const char *path);
+
+/* Per-kernel measurements of a render started with config.profile != 0. */
+#define B200PT_K_RAYGEN 0
+#define B200PT_K_EXTEND 1
+#define B200PT_K_SHADE 2
+#define B200PT_K_NEE 3
+#define B200PT_K_ACCUMULATE 4
+#define B200PT_K_COUNT 5
+typedef struct b200pt_profile {
+    double ms[B200PT_K_COUNT];        /* profile == 1: device time per kernel class, summed over launches */
+    int64_t launches[B200PT_K_COUNT]; /* kernel launches per class so far (always counted) */
+    /* profile == 2: traversal work of the extension rays (k_extend) and of the shadow rays (k_nee) */
+    uint64_t ext_rays, ext_boxes, ext_prims;
+    uint64_t nee_rays, nee_boxes, nee_prims;
+} b200pt_profile;
+int b200pt_render_profile(b200pt_render *render, b200pt_profile *out);
+
 void b200pt_render_destroy(b200pt_render *render);
 
 #ifdef __cplusplus

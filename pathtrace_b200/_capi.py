@@ -57,7 +57,7 @@ class Config(C.Structure):
                 ("only_direct_illumination", C.c_int32), ("normal_offset", C.c_float),
                 ("block_width", C.c_int32), ("block_height", C.c_int32), ("threads", C.c_int32),
                 ("seed", C.c_uint64), ("sample_offset", C.c_int64), ("device", C.c_int32),
-                ("batch_samples", C.c_int32), ("stats_clamp", C.c_float)]
+                ("batch_samples", C.c_int32), ("stats_clamp", C.c_float), ("profile", C.c_int32)]
 
 
 class Progress(C.Structure):
@@ -65,6 +65,14 @@ class Progress(C.Structure):
                 ("rays_shadow", C.c_int64), ("rays_reference", C.c_int64), ("seconds", C.c_double),
                 ("done", C.c_int32)]
 
+
+class Profile(C.Structure):
+    _fields_ = [("ms", C.c_double * 5), ("launches", C.c_int64 * 5),
+                ("ext_rays", C.c_uint64), ("ext_boxes", C.c_uint64), ("ext_prims", C.c_uint64),
+                ("nee_rays", C.c_uint64), ("nee_boxes", C.c_uint64), ("nee_prims", C.c_uint64)]
+
+
+KERNEL_NAMES = ("raygen", "extend", "shade", "nee", "accumulate")
 
 HIT_DTYPE = np.dtype([("instance", "<i4"), ("t", "<f4"), ("p", "<f4", 3), ("n", "<f4", 3), ("u", "<f4"), ("v", "<f4")])
 assert HIT_DTYPE.itemsize == 40
@@ -91,6 +99,7 @@ SIGNATURES = {
     "b200pt_render_write": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
     "b200pt_render_tonemap": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "b200pt_render_write_ppm": (C.c_int, [C.c_void_p, C.c_int64, C.c_char_p]),
+    "b200pt_render_profile": (C.c_int, [C.c_void_p, C.POINTER(Profile)]),
     "b200pt_render_destroy": (None, [C.c_void_p]),
 }
 

@@ -154,11 +154,37 @@ struct b200pt_render {
     int n_rows = 0;
     double seconds = 0.0;
     int64_t spp_done = 0;
+    // config.profile: per-class launch counts, event pairs of the launches enqueued since the last sync
+    b200pt_profile prof{};
+    struct Timed {
+        int cls;
+        cudaEvent_t a, b;
+    };
+    std::vector<Timed> pending;
+    std::vector<cudaEvent_t> event_pool;
+
+    cudaEvent_t get_event()
+    {
+        if (!event_pool.empty()) {
+            cudaEvent_t e = event_pool.back();
+            event_pool.pop_back();
+            return e;
+        }
+        cudaEvent_t e = nullptr;
+        cudaEventCreate(&e);
+        return e;
+    }
 
     ~b200pt_render()
     {
         if (scene)
             cudaSetDevice(scene->device);
+        for (auto &t : pending) {
+            cudaEventDestroy(t.a);
+            cudaEventDestroy(t.b);
+        }
+        for (cudaEvent_t e : event_pool)
+            cudaEventDestroy(e);
         for (void *p : allocations)
             cudaFree(p);
         if (ev0)
@@ -180,22 +206,53 @@ template <typename T> T *render_alloc(b200pt_render &r, size_t count, bool zero 
     return p;
 }
 
+// one kernel launch (or a short group of one class), counted and -- with config.profile == 1 -- bracketed by events
+template <typename F> void launch_class(b200pt_render &r, int cls, int n_launches, F &&f)
+{
+    cudaStream_t st = r.scene->stream;
+    r.prof.launches[cls] += n_launches;
+    if (r.cfg.profile != 1) {
+        f();
+        return;
+    }
+    b200pt_render::Timed t{cls, r.get_event(), r.get_event()};
+    CK(cudaEventRecord(t.a, st));
+    f();
+    CK(cudaEventRecord(t.b, st));
+    r.pending.push_back(t);
+}
+
+void collect_kernel_times(b200pt_render &r)
+{
+    for (auto &t : r.pending) {
+        float ms = 0.f;
+        CK(cudaEventSynchronize(t.b));
+        CK(cudaEventElapsedTime(&ms, t.a, t.b));
+        r.prof.ms[t.cls] += ms;
+        r.event_pool.push_back(t.a);
+        r.event_pool.push_back(t.b);
+    }
+    r.pending.clear();
+}
+
 void enqueue_batch(b200pt_render &r)
 {
     cudaStream_t st = r.scene->stream;
     const pt::PtSceneView &s = r.scene->view;
     CK(cudaMemsetAsync(r.wf.counters, 0, sizeof(int32_t) * pt::CNT_ROW * r.n_rows, st));
-    pt::launch_raygen(s, r.rp, r.wf, r.lc, st);
+    launch_class(r, B200PT_K_RAYGEN, 1, [&] { pt::launch_raygen(s, r.rp, r.wf, r.lc, st); });
     const bool nee = r.cfg.integrator == B200PT_INTEGRATOR_INEEPT;
     const int n_bounces = nee ? r.cfg.max_bounces : r.cfg.max_bounces + 1;
     for (int b = 0; b < n_bounces; b++) {
-        pt::launch_extend(s, r.rp, r.wf, b, r.lc, st);
-        for (int k = 0; k < pt::SK_COUNT; k++)
-            pt::launch_shade(s, r.rp, r.wf, b, k, r.lc, st);
+        launch_class(r, B200PT_K_EXTEND, 1, [&] { pt::launch_extend(s, r.rp, r.wf, b, r.lc, st); });
+        launch_class(r, B200PT_K_SHADE, pt::SK_COUNT, [&] {
+            for (int k = 0; k < pt::SK_COUNT; k++)
+                pt::launch_shade(s, r.rp, r.wf, b, k, r.lc, st);
+        });
         if (nee)
-            pt::launch_nee(s, r.rp, r.wf, b, r.lc, st);
+            launch_class(r, B200PT_K_NEE, 1, [&] { pt::launch_nee(s, r.rp, r.wf, b, r.lc, st); });
     }
-    pt::launch_accumulate(r.rp, r.wf, r.film, n_bounces, st);
+    launch_class(r, B200PT_K_ACCUMULATE, 2, [&] { pt::launch_accumulate(r.rp, r.wf, r.film, n_bounces, st); });
     CK(cudaGetLastError());
 }
 
@@ -441,6 +498,7 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         r->n_rows = c.max_bounces + 3;
         wf.counters = render_alloc<int32_t>(*r, (size_t)pt::CNT_ROW * r->n_rows, true);
         wf.ctl = render_alloc<pt::BatchCtl>(*r, 1, true);
+        wf.trace_counts = render_alloc<unsigned long long>(*r, 6, true);
         pt::BatchCtl ctl{};
         ctl.sample_base = c.sample_offset;
         ctl.nsamp = bs;
@@ -462,6 +520,7 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         cudaDeviceProp prop;
         CK(cudaGetDeviceProperties(&prop, scene->device));
         r->lc.threads = 256;
+        r->lc.count_work = c.profile == 2;
         r->lc.blocks = prop.multiProcessorCount * 8;
         *out = r.release();
     });
@@ -487,6 +546,7 @@ int b200pt_render_poll(b200pt_render *r, int32_t max_batches, b200pt_progress *p
             CK(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
             r->seconds += ms * 1e-3;
             r->batches_done += todo;
+            collect_kernel_times(*r);
         }
         pt::BatchCtl ctl;
         CK(cudaMemcpyAsync(&ctl, r->wf.ctl, sizeof(ctl), cudaMemcpyDeviceToHost, st));
@@ -612,6 +672,21 @@ int b200pt_render_write_ppm(b200pt_render *r, int64_t n_samples, const char *pat
     f << "P6\n" << r->cfg.width << " " << r->cfg.height << "\n255\n";
     f.write((const char *)rgb.data(), (std::streamsize)rgb.size());
     return f.good() ? B200PT_OK : fail(B200PT_ERR_INVALID, std::string("write failed: ") + path);
+}
+
+int b200pt_render_profile(b200pt_render *r, b200pt_profile *out)
+{
+    if (!r || !out)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    return guarded([&] {
+        need_device(r->scene);
+        unsigned long long h[6];
+        CK(cudaMemcpyAsync(h, r->wf.trace_counts, sizeof(h), cudaMemcpyDeviceToHost, r->scene->stream));
+        CK(cudaStreamSynchronize(r->scene->stream));
+        *out = r->prof;
+        out->ext_rays = h[0], out->ext_boxes = h[1], out->ext_prims = h[2];
+        out->nee_rays = h[3], out->nee_boxes = h[4], out->nee_prims = h[5];
+    });
 }
 
 void b200pt_render_destroy(b200pt_render *r) { delete r; }

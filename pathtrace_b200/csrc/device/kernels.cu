@@ -58,6 +58,22 @@ __device__ __forceinline__ void block_reserve(unsigned mask, int32_t *const (&co
     __syncthreads();
 }
 
+// work counters of one thread -> global totals (profile == 2 only)
+__device__ __forceinline__ void flush_counts(const TraceCounters &tc, unsigned long long rays, unsigned long long *dst)
+{
+    unsigned long long b = tc.boxes, p = tc.prims, r = rays;
+    for (int off = 16; off > 0; off >>= 1) {
+        b += __shfl_down_sync(0xffffffffu, b, off);
+        p += __shfl_down_sync(0xffffffffu, p, off);
+        r += __shfl_down_sync(0xffffffffu, r, off);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(dst + 0, r);
+        atomicAdd(dst + 1, b);
+        atomicAdd(dst + 2, p);
+    }
+}
+
 __device__ __forceinline__ RngKey make_key(const RenderParams &rp, const Wavefront &wf, int slot, long long sample_base)
 {
     RngKey k;
@@ -103,8 +119,12 @@ __global__ void __launch_bounds__(kThreads) k_raygen(PtSceneView s, RenderParams
     }
 }
 
+template <bool COUNT>
 __global__ void __launch_bounds__(kThreads) k_extend(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
+    TraceCounters tc;
+    tc.boxes = tc.prims = 0;
+    unsigned long long nrays = 0;
     const long long sample_base = wf.ctl->sample_base;
     int32_t *row = wf.counters + bounce * CNT_ROW;
     const int n = row[CNT_EXT];
@@ -124,7 +144,8 @@ __global__ void __launch_bounds__(kThreads) k_extend(PtSceneView s, RenderParams
             mr.xi = -1.f;
             Hit h;
             int kind = SK_MISS;
-            if (trace_closest<false>(s, xyz(ro), xyz(rd), 0.001f, PT_FLT_MAX, mr, h, nullptr)) {
+            nrays++;
+            if (trace_closest<COUNT>(s, xyz(ro), xyz(rd), 0.001f, PT_FLT_MAX, mr, h, &tc)) {
                 wf.hit_p[slot] = f4(h.p, __int_as_float(h.inst));
                 wf.hit_n[slot] = f4(h.n, h.t);
                 kind = shade_kind_of(s.mats[meta_material(s.inst[h.inst].meta)].kind);
@@ -138,6 +159,8 @@ __global__ void __launch_bounds__(kThreads) k_extend(PtSceneView s, RenderParams
             wf.q_kind[kind][pos[kind]] = slot;
         }
     }
+    if (COUNT)
+        flush_counts(tc, nrays, wf.trace_counts);
 }
 
 __global__ void __launch_bounds__(kThreads) k_shade(PtSceneView s, RenderParams rp, Wavefront wf, int bounce, int kind)
@@ -210,8 +233,12 @@ __global__ void __launch_bounds__(kThreads) k_shade(PtSceneView s, RenderParams 
 // One thread per (vertex, light sample).  With light_samples a power of two <= 32 the samples of one vertex sit in
 // adjacent lanes: same origin, nearly the same target -> coherent traversal, and the sum is a fixed-order shuffle
 // reduction; otherwise float atomics.
+template <bool COUNT>
 __global__ void __launch_bounds__(kThreads) k_nee(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
+    TraceCounters tc;
+    tc.boxes = tc.prims = 0;
+    unsigned long long nrays = 0;
     const long long sample_base = wf.ctl->sample_base;
     const int L = rp.light_samples;
     const long long n = (long long)wf.counters[bounce * CNT_ROW + CNT_NEE] * L;
@@ -226,7 +253,8 @@ __global__ void __launch_bounds__(kThreads) k_nee(PtSceneView s, RenderParams rp
             slot = wf.q_nee[q];
             float4 hp = wf.hit_p[slot], hn = wf.hit_n[slot], w = wf.nee_w[slot];
             RngKey key = make_key(rp, wf, slot, sample_base);
-            c = nee_sample<false>(s, rp, key, bounce, k, xyz(hp), xyz(hn), __float_as_int(w.w), xyz(w), nullptr);
+            nrays++;
+            c = nee_sample<COUNT>(s, rp, key, bounce, k, xyz(hp), xyz(hn), __float_as_int(w.w), xyz(w), &tc);
         }
         if (pow2) {
             // lanes [g*L, (g+1)*L) hold one vertex (kThreads and 32 are multiples of L)
@@ -250,6 +278,8 @@ __global__ void __launch_bounds__(kThreads) k_nee(PtSceneView s, RenderParams rp
                 atomicAdd(dst + 2, c.z / inv_L_div);
         }
     }
+    if (COUNT)
+        flush_counts(tc, nrays, wf.trace_counts + 3);
 }
 
 // framebuffer[j][i] += de_nan(col): one thread per pixel walks the samples of the batch in order, so the film is
@@ -457,7 +487,10 @@ void launch_raygen(const PtSceneView &s, const RenderParams &rp, const Wavefront
 void launch_extend(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, const LaunchCfg &lc,
                    cudaStream_t st)
 {
-    k_extend<<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+    if (lc.count_work)
+        k_extend<true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+    else
+        k_extend<false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
 }
 
 void launch_shade(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, int kind,
@@ -469,7 +502,10 @@ void launch_shade(const PtSceneView &s, const RenderParams &rp, const Wavefront 
 void launch_nee(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, const LaunchCfg &lc,
                 cudaStream_t st)
 {
-    k_nee<<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+    if (lc.count_work)
+        k_nee<true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+    else
+        k_nee<false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
 }
 
 void launch_accumulate(const RenderParams &rp, const Wavefront &wf, const Film &film, int n_rows, cudaStream_t st)

@@ -43,6 +43,7 @@ struct Wavefront {
     int32_t *q_nee;
     int32_t *counters; // (max_bounces + 2) rows of CNT_ROW
     BatchCtl *ctl;
+    unsigned long long *trace_counts; // profile == 2: {ext rays, boxes, prims, nee rays, boxes, prims}
     int32_t npix;
     int32_t capacity; // slots
 };
@@ -57,6 +58,7 @@ struct Film {
 struct LaunchCfg {
     int blocks;  // grid size for the queue-driven kernels (persistent, grid-stride)
     int threads; // 256
+    bool count_work; // run the traversal kernels with work counters on (config.profile == 2)
 };
 
 void launch_raygen(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, const LaunchCfg &lc, cudaStream_t st);

@@ -252,6 +252,15 @@ class Wavefront:
         check(lib().b200pt_render_read_stats(self._h, s.ctypes.data, q.ctypes.data))
         return s, q
 
+    def profile(self):
+        """Per-kernel device time / launch counts / traversal work counters (config.profile)."""
+        p = _capi.Profile()
+        check(lib().b200pt_render_profile(self._h, C.byref(p)))
+        out = {"ms": dict(zip(_capi.KERNEL_NAMES, p.ms[:])), "launches": dict(zip(_capi.KERNEL_NAMES, p.launches[:]))}
+        for k in ("ext_rays", "ext_boxes", "ext_prims", "nee_rays", "nee_boxes", "nee_prims"):
+            out[k] = getattr(p, k)
+        return out
+
     def device_buffer(self):
         p, n = C.c_void_p(), C.c_size_t()
         check(lib().b200pt_render_device_buffer(self._h, C.byref(p), C.byref(n)))

@@ -1,0 +1,170 @@
+"""Parity check 2, GPU side: renders through the C ABI against the CPU restatement, which draws the
+same Philox variates -- so the comparison is per SAMPLE SUM, not statistical: it checks the wavefront plumbing
+(queues, compaction, material sort, batching, accumulation order).  The restatement itself is pinned against the
+unmodified reference in tests/test_oracle_vs_reference.py (CPU) and test_render_matches_reference_golden below."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import scene_path
+from oracle_lib import PortOracle, make_cconfig
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _render(cfgd, **over):
+    import pathtrace_b200 as pt
+    cfg = pt.Config.from_json(cfgd)
+    if over:
+        cfg = cfg.replace(**over)
+    scene = pt.Scene.from_file(cfg.scene_path, cfg.width, cfg.height, device=0)
+    r = pt.renderer_from_config(scene, cfg).start_render()
+    rep = r.finalize()
+    return r, rep
+
+
+def _cfg(scene, w, h, spp, **kw):
+    import pathtrace_b200 as pt
+    return pt.default_config_dict(width=w, height=h, samples=spp, scene=scene_path(scene), **kw)
+
+
+def _close(a, b, what):
+    """Sample sums agree up to libm ulps amplified through a few bounces; a plumbing error shows up as O(1)."""
+    scale = np.maximum(np.abs(b), 1e-3 * max(1.0, float(np.abs(b).max())))
+    rel = np.abs(a - b) / scale
+    frac_bad = float((rel > 1e-3).mean())
+    assert frac_bad < 1e-2, (what, frac_bad, float(rel.max()))
+    tot_a, tot_b = float(a.astype(np.float64).sum()), float(b.astype(np.float64).sum())
+    assert abs(tot_a - tot_b) <= 1e-2 * abs(tot_b) + 1e-6, (what, tot_a, tot_b)
+
+
+CASES = [
+    ("three_orbs", dict()),
+    ("cornell_box", dict()),
+    ("cornell_box_small_lights", dict(light_samples=3)),
+    ("cornell_box_with_volume", dict()),
+    ("cornell_box_with_volume2", dict(russian_roulette=False, max_bounces=4)),
+    ("light_test", dict(light_samples=1)),
+    ("book2_final", dict()),
+    ("cornell_box", dict(integrator_type="recursive path tracing")),
+    ("three_orbs", dict(integrator_type="recursive path tracing", max_bounces=5)),
+    ("cornell_box", dict(only_direct_illumination=True)),
+    ("cornell_box", dict(max_bounces=1)),
+]
+
+
+@pytest.mark.parametrize("scene,over", CASES)
+def test_render_matches_cpu_restatement(scene, over):
+    w, h, spp = 48, 40, 6
+    cfgd = _cfg(scene, w, h, spp, **over)
+    r, rep = _render(cfgd, batch_samples=4)  # 2 batches: 4 + 2 samples
+    fb = r.framebuffer
+    oracle = PortOracle.from_file(scene_path(scene), w, h)
+    ref = oracle.render(make_cconfig(cfgd), stats=False)
+    _close(fb, ref["sums"], scene)
+    # ray accounting: a differing libm ulp can flip a Russian-roulette or medium decision on a handful of paths
+    for k in ("rays_extension", "rays_shadow", "rays_reference"):
+        assert abs(rep[k] - ref[k]) <= 2e-3 * ref[k] + 8, (k, rep[k], ref[k])
+    assert rep["camera_rays"] == w * h * spp
+
+
+def test_batching_and_sharding_invariance():
+    """Philox is keyed on (pixel, GLOBAL sample): the film does not depend on the batch size, and two spp shards
+    (sample_offset) add up to the unsharded film -- what multi-GPU sharding relies on."""
+    w, h, spp = 64, 48, 8
+    cfgd = _cfg("cornell_box", w, h, spp)
+    a = _render(cfgd, batch_samples=1)[0].framebuffer
+    b = _render(cfgd, batch_samples=8)[0].framebuffer
+    assert np.array_equal(a, b)
+    half = dict(cfgd, samples=spp // 2)
+    s0 = _render(half, sample_offset=0)[0].framebuffer
+    s1 = _render(half, sample_offset=spp // 2)[0].framebuffer
+    np.testing.assert_allclose(s0 + s1, a, rtol=1e-5, atol=1e-6)
+    c = _render(cfgd, seed=123)[0].framebuffer
+    assert not np.array_equal(a, c)
+
+
+def test_stats_buffers():
+    w, h, spp = 32, 32, 16
+    cfgd = _cfg("cornell_box", w, h, spp)
+    r, _ = _render(cfgd, stats_clamp=2.0)
+    s, q = r.stats()
+    oracle = PortOracle.from_file(scene_path("cornell_box"), w, h)
+    ref = oracle.render(make_cconfig(cfgd, stats_clamp=2.0))
+    _close(s, ref["csum"], "csum")
+    _close(q, ref["csq"], "csq")
+    assert float(s.max()) <= 2.0 * spp + 1e-3
+
+
+def _tonemap_numpy(fb, n, exposure):
+    """output_to_file + calculate_luminance (renderer.h:24-55, helpers.h:78-93,146-168, tonemap.h:4-24) in numpy fp32."""
+    f32 = np.float32
+    inv_n = f32(1.0 / float(f32(n)))
+    c = np.where(np.isnan(fb), f32(0), fb).astype(f32) * inv_n
+    lum = np.sqrt((c.astype(np.float64) ** 2).sum(-1))
+    max_lum = f32(lum.max())
+
+    def u2(x):
+        A, B, C, D, E, F = map(f32, (0.15, 0.50, 0.10, 0.20, 0.02, 0.30))
+        return ((x * (A * x + C * B) + D * E) / (x * (A * x + B) + D * F)) - E / F
+
+    x = fb.astype(f32) * inv_n * f32(16 + exposure)
+    x = np.clip(u2(x) / u2(max_lum), 0, 1).astype(f32)
+    srgb = np.where(x < f32(0.0031308), f32(323) * x / f32(25), (f32(211) * np.power(x, f32(5.0 / 12)) - f32(11)) / f32(200))
+    img = (f32(255) * srgb.astype(f32)).astype(np.int32).astype(np.uint8)
+    return img[::-1], float(max_lum)
+
+
+def test_tonemap_and_ppm(tmp_path):
+    w, h, spp = 40, 24, 4
+    cfgd = _cfg("cornell_box", w, h, spp)
+    r, _ = _render(cfgd)
+    fb = r.framebuffer
+    img, mx, avg = r.tonemap()
+    exp_img, exp_max = _tonemap_numpy(fb, spp, r.config.exposure)
+    assert abs(mx - exp_max) <= 1e-5 * exp_max
+    diff = np.abs(img.astype(np.int32) - exp_img.astype(np.int32))
+    assert diff.max() <= 1 and (diff > 0).mean() < 0.01  # truncation to bytes: an ulp in powf can move one level
+    path = str(tmp_path / "out" / "render.ppm")
+    r.write_ppm(path)
+    with open(path, "rb") as f:
+        data = f.read()
+    header = f"P6\n{w} {h}\n255\n".encode()
+    assert data.startswith(header) and len(data) == len(header) + w * h * 3
+    assert np.array_equal(np.frombuffer(data[len(header):], dtype=np.uint8).reshape(h, w, 3), img)
+    assert abs(r.config.exposure - 2.2) < 1e-6  # Q1: JSON "gamma" lands in film.exposure (config.h:24-25)
+
+
+@pytest.mark.parametrize("tag", ["cornell_box_d1", "cornell_box_b3", "cornell_box_rpt", "three_orbs_full",
+                                 "cornell_box_small_lights_d1", "cornell_box_with_volume_b2", "light_test_b2",
+                                 "book2_final_b2"])
+def test_render_matches_reference_golden(tag):
+    """Statistical parity with the UNMODIFIED reference: golden per-pixel statistics of integrator->color made by
+    tests/golden/make_golden.py (ref_driver `color` mode).  Clamped samples on both sides (finite variance)."""
+    path = os.path.join(GOLDEN, f"color_{tag}.npz")
+    if not os.path.exists(path):
+        pytest.skip("no golden file")
+    g = np.load(path, allow_pickle=False)
+    cfgd = json.loads(str(g["config"]))
+    cfgd["scene"] = scene_path(os.path.basename(cfgd["scene"]).replace(".json", ""))
+    n_ref, clamp = int(g["n"]), float(g["clamp"])
+    n_gpu = 4096
+    cfgd["samples"] = n_gpu
+    r, _ = _render(cfgd, stats_clamp=clamp, seed=77)
+    s, q = r.stats()
+    mean_g = s.astype(np.float64) / n_gpu
+    var_g = np.maximum(q.astype(np.float64) / n_gpu - mean_g ** 2, 0) * n_gpu / (n_gpu - 1)
+    mean_r = g["cmean"]
+    var_r = g["cm2"] / (n_ref - 1)
+    se = np.sqrt(var_g / n_gpu + var_r / n_ref)
+    ok = se > 0
+    z = (mean_g[ok] - mean_r[ok]) / se[ok]
+    assert abs(z.mean()) < 0.2, z.mean()  # skewed samples bias z by O(skew / sqrt(n)): not exactly 0
+    assert (np.abs(z) > 3).mean() < 0.02, (np.abs(z) > 3).mean()
+    assert (np.abs(z) > 6).mean() < 1e-3, np.abs(z).max()
+    # deterministic pixels (zero variance on both sides) must agree outright
+    np.testing.assert_allclose(mean_g[~ok], mean_r[~ok], rtol=1e-4, atol=1e-6)

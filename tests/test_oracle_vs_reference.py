@@ -1,0 +1,91 @@
+"""Pins the CPU restatement (oracle/pt_oracle.cpp) against the UNMODIFIED reference on the CPU:
+  * closest-hit records: bit-exact against the committed golden vectors (and against a live ref_driver run when the
+    binary is present) -- ids, t, p, normal;
+  * renders: per-pixel statistics of integrator->color (golden, tests/golden/make_golden.py) against the
+    restatement's own samples, clamped on both sides so the variance is finite.
+The restatement uses Philox, the reference mt19937: render parity is statistical by construction."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import raygen
+import scene_match
+from conftest import SCENE_FILES, scene_path
+from oracle_lib import PortOracle, RefDriver, have_ref_driver, make_cconfig
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+W, H = 32, 18
+
+
+def _flat(name):
+    import pathtrace_b200 as pt
+    return pt.Scene.from_file(scene_path(name), W, H, device=-1)
+
+
+@pytest.mark.parametrize("name", SCENE_FILES)
+def test_hits_match_golden_bitwise(name):
+    g = np.load(os.path.join(GOLDEN, f"hits_{name}.npz"))
+    flat = _flat(name).describe()
+    media = [i for i, s in enumerate(flat["instances"]) if s["flags"] & 1]
+    got = PortOracle.from_file(scene_path(name), W, H).trace(g["rays"], np.full(len(g["rays"]), 0.5, np.float32))
+    keep = ~np.isin(g["instance"], media) & ~np.isin(got["instance"], media)  # media are stochastic in the reference
+    assert keep.sum() > 0.5 * len(keep)
+    assert np.array_equal(got["instance"][keep], g["instance"][keep])
+    hit = keep & (g["instance"] >= 0)
+    for f in ("t", "p", "n"):
+        assert np.array_equal(got[f][hit], g[f][hit]), f
+    rect = hit & np.isin(g["instance"], [i for i, s in enumerate(flat["instances"]) if s["prim_kind"] == 1])
+    assert np.array_equal(got["u"][rect], g["u"][rect]) and np.array_equal(got["v"][rect], g["v"][rect])
+
+
+@pytest.mark.parametrize("name", ["cornell_box", "three_orbs", "book2_final"])
+def test_hits_match_live_reference(name):
+    if not have_ref_driver():
+        pytest.skip("oracle/_ref/ref_driver not built")
+    sc = _flat(name)
+    flat = sc.describe()
+    mapping, worst = scene_match.match_leaves(RefDriver.scene(scene_path(name), W, H), flat)
+    assert worst < 1e-6
+    b = sc.bvh_info()["bounds"]
+    rays = raygen.random_rays(b[:3], b[3:], 30000, seed=9)
+    ref = scene_match.remap_ref_hits(RefDriver.hit(scene_path(name), rays), mapping)
+    got = PortOracle.from_file(scene_path(name), W, H).trace(rays, np.full(len(rays), 0.5, np.float32))
+    media = [i for i, s in enumerate(flat["instances"]) if s["flags"] & 1]
+    st = raygen.compare_hits(ref, got, exclude_instances=media)
+    assert st["id_agree"] == 1.0 and st["t_rel_max"] == 0.0 and st["n_err_max"] == 0.0 and st["p_rel_max"] == 0.0, st
+
+
+def z_scores(mean_a, var_a, n_a, mean_b, var_b, n_b):
+    se = np.sqrt(var_a / n_a + var_b / n_b)
+    ok = se > 0
+    return (mean_a[ok] - mean_b[ok]) / se[ok], ok
+
+
+COLOR_TAGS = ["cornell_box_d1", "cornell_box_b3", "cornell_box_rpt", "three_orbs_full", "cornell_box_small_lights_d1",
+              "cornell_box_with_volume_b2", "light_test_b2", "book2_final_b2"]
+
+
+@pytest.mark.parametrize("tag", COLOR_TAGS)
+def test_render_statistics_match_reference(tag):
+    g = np.load(os.path.join(GOLDEN, f"color_{tag}.npz"))
+    cfgd = json.loads(str(g["config"]))
+    name = os.path.basename(cfgd["scene"]).replace(".json", "")
+    cfgd["scene"] = scene_path(name)
+    n_ref, clamp = int(g["n"]), float(g["clamp"])
+    n = 2048
+    cfgd["samples"] = n
+    w, h = cfgd["film"]["width"], cfgd["film"]["height"]
+    out = PortOracle.from_file(cfgd["scene"], w, h).render(make_cconfig(cfgd, stats_clamp=clamp, seed=4242))
+    mean = out["csum"].astype(np.float64) / n
+    var = np.maximum(out["csq"].astype(np.float64) / n - mean ** 2, 0) * n / (n - 1)
+    z, ok = z_scores(mean, var, n, g["cmean"], g["cm2"] / (n_ref - 1), n_ref)
+    assert abs(z.mean()) < 0.2, z.mean()  # skewed samples bias z by O(skew / sqrt(n)): not exactly 0
+    assert (np.abs(z) > 3).mean() < 0.02, (np.abs(z) > 3).mean()
+    assert (np.abs(z) > 6).mean() < 1e-3, np.abs(z).max()
+    np.testing.assert_allclose(mean[~ok], g["cmean"][~ok], rtol=1e-4, atol=1e-6)
+    # ray accounting follows the reference's bounce counter (integrator.h:192,247) within sampling noise
+    ref_rays_per_path = float(g["total_rays"]) / (w * h * n_ref)
+    got = out["rays_reference"] / (w * h * n)
+    assert abs(got - ref_rays_per_path) < 0.03 * ref_rays_per_path, (got, ref_rays_per_path)
