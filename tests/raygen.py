@@ -88,6 +88,12 @@ def compare_hits(ref, got, exclude_instances=()):
         keep &= (ref["instance"] != e) & (got["instance"] != e)
     same = ref["instance"] == got["instance"]
     both = same & (ref["instance"] >= 0) & keep
+    # a ray lying IN a rect's plane gives t = 0/0 = NaN, which passes `t < t0 || t > t1` (primitive.h:196) in the
+    # reference and here alike: such records agree when both sides hold NaN
+    nan_both = np.isnan(ref["t"]) & np.isnan(got["t"])
+    nan_one = np.isnan(ref["t"]) ^ np.isnan(got["t"])
+    n_nan_mismatch = int((nan_one & both).sum())
+    both = both & ~nan_both & ~nan_one
     t_ref = ref["t"][both].astype(np.float64)
     dt = np.abs(got["t"][both].astype(np.float64) - t_ref) / np.maximum(np.abs(t_ref), 1e-30)
     dn = np.linalg.norm(got["n"][both].astype(np.float64) - ref["n"][both].astype(np.float64), axis=1)
@@ -97,6 +103,7 @@ def compare_hits(ref, got, exclude_instances=()):
         "n": int(keep.sum()),
         "id_agree": float((same & keep).sum() / max(1, keep.sum())),
         "n_hit": int(both.sum()),
+        "nan_mismatch": n_nan_mismatch,
         "t_rel_max": float(dt.max()) if len(dt) else 0.0,
         "t_rel_p9999": float(np.quantile(dt, 0.9999)) if len(dt) else 0.0,
         "t_bad": float((dt > 1e-5).mean()) if len(dt) else 0.0,
