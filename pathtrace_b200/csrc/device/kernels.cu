@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(kThreads) k_raygen(PtSceneView s, RenderParams
     }
 }
 
-template <bool COUNT>
+template <bool COUNT, bool MEDIA>
 __global__ void __launch_bounds__(kThreads) k_extend(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
     TraceCounters tc;
@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(kThreads) k_extend(PtSceneView s, RenderParams
             Hit h;
             int kind = SK_MISS;
             nrays++;
-            if (trace_closest<COUNT>(s, xyz(ro), xyz(rd), 0.001f, PT_FLT_MAX, mr, h, &tc)) {
+            if (trace_closest<COUNT, MEDIA>(s, xyz(ro), xyz(rd), 0.001f, PT_FLT_MAX, mr, h, &tc)) {
                 wf.hit_p[slot] = f4(h.p, __int_as_float(h.inst));
                 wf.hit_n[slot] = f4(h.n, h.t);
                 kind = shade_kind_of(s.mats[meta_material(s.inst[h.inst].meta)].kind);
@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(kThreads) k_shade(PtSceneView s, RenderParams 
 // One thread per (vertex, light sample).  With light_samples a power of two <= 32 the samples of one vertex sit in
 // adjacent lanes: same origin, nearly the same target -> coherent traversal, and the sum is a fixed-order shuffle
 // reduction; otherwise float atomics.
-template <bool COUNT>
+template <bool COUNT, bool MEDIA>
 __global__ void __launch_bounds__(kThreads) k_nee(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
     TraceCounters tc;
@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(kThreads) k_nee(PtSceneView s, RenderParams rp
             float4 hp = wf.hit_p[slot], hn = wf.hit_n[slot], w = wf.nee_w[slot];
             RngKey key = make_key(rp, wf, slot, sample_base);
             nrays++;
-            c = nee_sample<COUNT>(s, rp, key, bounce, k, xyz(hp), xyz(hn), __float_as_int(w.w), xyz(w), &tc);
+            c = nee_sample<COUNT, MEDIA>(s, rp, key, bounce, k, xyz(hp), xyz(hn), __float_as_int(w.w), xyz(w), &tc);
         }
         if (pow2) {
             // lanes [g*L, (g+1)*L) hold one vertex (kThreads and 32 are multiples of L)
@@ -350,7 +350,7 @@ __global__ void k_tally(RenderParams rp, Wavefront wf, int n_rows)
 
 // ---------------------------------------------------------------------------------------------------------------
 
-template <bool COUNT>
+template <bool COUNT, bool MEDIA>
 __global__ void __launch_bounds__(kThreads) k_trace_batch(PtSceneView s, const float *__restrict__ rays, size_t n,
                                                           const float *__restrict__ medium_xi,
                                                           b200pt_hit *__restrict__ hits, unsigned long long *counts)
@@ -369,7 +369,7 @@ __global__ void __launch_bounds__(kThreads) k_trace_batch(PtSceneView s, const f
         Hit h;
         TraceCounters tc;
         tc.boxes = tc.prims = 0;
-        bool ok = trace_closest<COUNT>(s, v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), b.z, b.w, mr, h, &tc);
+        bool ok = trace_closest<COUNT, MEDIA>(s, v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), b.z, b.w, mr, h, &tc);
         if (COUNT) {
             boxes += tc.boxes;
             prims += tc.prims;
@@ -488,9 +488,11 @@ void launch_extend(const PtSceneView &s, const RenderParams &rp, const Wavefront
                    cudaStream_t st)
 {
     if (lc.count_work)
-        k_extend<true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+        k_extend<true, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+    else if (s.n_media > 0)
+        k_extend<false, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
     else
-        k_extend<false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+        k_extend<false, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
 }
 
 void launch_shade(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, int kind,
@@ -503,9 +505,11 @@ void launch_nee(const PtSceneView &s, const RenderParams &rp, const Wavefront &w
                 cudaStream_t st)
 {
     if (lc.count_work)
-        k_nee<true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+        k_nee<true, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+    else if (s.n_media > 0)
+        k_nee<false, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
     else
-        k_nee<false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+        k_nee<false, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
 }
 
 void launch_accumulate(const RenderParams &rp, const Wavefront &wf, const Film &film, int n_rows, cudaStream_t st)
@@ -523,9 +527,11 @@ void launch_trace_batch(const PtSceneView &s, const float *rays, size_t n, const
     size_t want = (n + kThreads - 1) / kThreads;
     int blocks = (int)(want < (size_t)(148 * 16) ? want : (size_t)(148 * 16));
     if (counts)
-        k_trace_batch<true><<<blocks, kThreads, 0, st>>>(s, rays, n, medium_xi, hits, counts);
+        k_trace_batch<true, true><<<blocks, kThreads, 0, st>>>(s, rays, n, medium_xi, hits, counts);
+    else if (s.n_media > 0)
+        k_trace_batch<false, true><<<blocks, kThreads, 0, st>>>(s, rays, n, medium_xi, hits, nullptr);
     else
-        k_trace_batch<false><<<blocks, kThreads, 0, st>>>(s, rays, n, medium_xi, hits, nullptr);
+        k_trace_batch<false, false><<<blocks, kThreads, 0, st>>>(s, rays, n, medium_xi, hits, nullptr);
 }
 
 void launch_luminance(const float4 *accum, int npix, float inv_n, float *max_total, cudaStream_t st)

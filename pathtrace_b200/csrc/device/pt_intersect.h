@@ -13,8 +13,8 @@ namespace pt {
 
 struct PrimHit {
     float t;
-    V3 n; // local-space normal
-    float u, v;
+    V3 n;     // local-space normal
+    int face; // box: index of the side that was hit (order of box::box, primitive.h:233-240); else 0
 };
 
 struct Hit {
@@ -52,8 +52,7 @@ PT_HD bool hit_sphere(V3 center, float radius, V3 o, V3 d, float t_min, float t_
         h.t = temp;
         V3 p = o + temp * d;
         h.n = (p - center) / radius;
-        h.u = 0.f; // left unset by the reference (Q11)
-        h.v = 0.f;
+        h.face = 0;
         return true;
     }
     return false;
@@ -71,9 +70,8 @@ PT_HD bool hit_rect(int plane, bool flip, float x0, float z0, float x1, float z1
     float zh = to.z + t * td.z;
     if (xh < x0 || xh > x1 || zh < z0 || zh > z1)
         return false;
-    h.u = (xh - x0) / (x1 - x0);
-    h.v = (zh - x0) / (z1 - z0); // sic: x0 (primitive.h:207)
-    h.t = t;
+    h.t = t; // rec.u / rec.v (primitive.h:206-207) are evaluated for the closest hit only: rect_uv()
+    h.face = 0;
     V3 n = shuffle(v3(0.f, flip ? -1.f : 1.f, 0.f), plane);
     if (dot(d, n) > 0) // two_sided is hard-wired true (primitive.h:181,214-222)
         n = -n;
@@ -81,44 +79,62 @@ PT_HD bool hit_rect(int plane, bool flip, float x0, float z0, float x1, float z1
     return true;
 }
 
+// rec.u, rec.v of a rect hit (primitive.h:206-207), from the same expressions as the hit test
+PT_HD void rect_uv(int plane, float x0, float z0, float x1, float z1, V3 o, V3 d, float t, float &u, float &v)
+{
+    V3 to = shuffle(o, plane);
+    V3 td = shuffle(d, plane);
+    float xh = to.x + t * td.x;
+    float zh = to.z + t * td.z;
+    u = (xh - x0) / (x1 - x0);
+    v = (zh - x0) / (z1 - z0); // sic: x0 (primitive.h:207)
+}
+
+// box::hit = hittable_list::hit over six rects (primitive.h:233-246, hittable_list.h:21-38): sides in the order
+// z = p0.z, z = p1.z, x = p0.x, x = p1.x, y = p0.y, y = p1.y; each is tested against [t_min, closest so far] with an
+// INCLUSIVE upper bound (rect::hit), so a later side at the same t replaces an earlier one.  One loop body serves
+// the three axis pairs by rotating (a, b, c) <- (b, c, a); every t and bound test is the rect's own expression.
 PT_HD bool hit_box(const float *p, V3 o, V3 d, float t_min, float t_max, PrimHit &h)
 {
-    // box::box builds sides in this order (primitive.h:233-240); hittable_list::hit keeps the last hit with
-    // t <= closest_so_far (inclusive upper bound in rect::hit).
-    bool any = false;
+    float oa = o.z, ob = o.x, oc = o.y, da = d.z, db = d.x, dc = d.y;
+    float la = p[2], lb = p[0], lc = p[1], ha = p[5], hb = p[3], hc = p[4];
     float closest = t_max;
-    PrimHit tmp;
-    if (hit_rect(B200PT_PLANE_XY, true, p[0], p[1], p[3], p[4], p[2], o, d, t_min, closest, tmp)) {
-        any = true;
-        closest = tmp.t;
-        h = tmp;
+    int face = -1;
+    float nsign = 0.f;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+    for (int it = 0; it < 3; it++) {
+        float t = (la - oa) / da;
+        if (!(t < t_min || t > closest)) { // NB a NaN t passes, as in the reference
+            float bh = ob + t * db, ch = oc + t * dc;
+            if (!(bh < lb || bh > hb || ch < lc || ch > hc)) {
+                closest = t;
+                face = 2 * it;
+                nsign = da < 0 ? 1.f : -1.f; // normal -e_a, turned to face the ray (primitive.h:214-222)
+            }
+        }
+        t = (ha - oa) / da;
+        if (!(t < t_min || t > closest)) {
+            float bh = ob + t * db, ch = oc + t * dc;
+            if (!(bh < lb || bh > hb || ch < lc || ch > hc)) {
+                closest = t;
+                face = 2 * it + 1;
+                nsign = da > 0 ? -1.f : 1.f;
+            }
+        }
+        float r;
+        r = oa, oa = ob, ob = oc, oc = r;
+        r = da, da = db, db = dc, dc = r;
+        r = la, la = lb, lb = lc, lc = r;
+        r = ha, ha = hb, hb = hc, hc = r;
     }
-    if (hit_rect(B200PT_PLANE_XY, false, p[0], p[1], p[3], p[4], p[5], o, d, t_min, closest, tmp)) {
-        any = true;
-        closest = tmp.t;
-        h = tmp;
-    }
-    if (hit_rect(B200PT_PLANE_YZ, true, p[1], p[2], p[4], p[5], p[0], o, d, t_min, closest, tmp)) {
-        any = true;
-        closest = tmp.t;
-        h = tmp;
-    }
-    if (hit_rect(B200PT_PLANE_YZ, false, p[1], p[2], p[4], p[5], p[3], o, d, t_min, closest, tmp)) {
-        any = true;
-        closest = tmp.t;
-        h = tmp;
-    }
-    if (hit_rect(B200PT_PLANE_XZ, true, p[0], p[2], p[3], p[5], p[1], o, d, t_min, closest, tmp)) {
-        any = true;
-        closest = tmp.t;
-        h = tmp;
-    }
-    if (hit_rect(B200PT_PLANE_XZ, false, p[0], p[2], p[3], p[5], p[4], o, d, t_min, closest, tmp)) {
-        any = true;
-        closest = tmp.t;
-        h = tmp;
-    }
-    return any;
+    if (face < 0)
+        return false;
+    h.t = closest;
+    h.face = face;
+    h.n = face < 2 ? v3(0.f, 0.f, nsign) : (face < 4 ? v3(nsign, 0.f, 0.f) : v3(0.f, nsign, 0.f));
+    return true;
 }
 
 // the bare primitive (sphere | rect | box) in its local frame
@@ -162,8 +178,7 @@ PT_HD bool hit_medium(uint32_t meta, const float *p, float density, V3 o, V3 d, 
     if (hit_distance < distance_inside_boundary) {
         h.t = ta + hit_distance / dlen;
         h.n = v3(1.f, 0.f, 0.f); // "arbitrary" (volume.h:86)
-        h.u = 0.f;
-        h.v = 0.f;
+        h.face = 0;
         return true;
     }
     return false;
@@ -207,11 +222,13 @@ PT_HD void load_instance(const PtInstance *table, int idx, InstanceData &I)
 }
 
 // instance::hit without the world-space epilogue: local ray, local hit record, t preserved (primitive.h:298-301).
+// MEDIA = false compiles the constant-medium branch out (scenes without volumes: smaller kernels).
+template <bool MEDIA>
 PT_HD bool hit_instance(const InstanceData &I, V3 o, V3 d, float t_min, float t_max, const MediumRng &mr, PrimHit &h)
 {
     V3 lo = xform_point(I.inv, o);
     V3 ld = xform_vector(I.inv, d);
-    if (!meta_medium(I.meta))
+    if (!MEDIA || !meta_medium(I.meta))
         return hit_prim(I.meta, I.p, lo, ld, t_min, t_max, h);
     float xi = mr.xi, xi2 = -1.f;
     if (xi < 0.f) {
@@ -256,7 +273,7 @@ struct TraceCounters {
 #define PT_STACK_DEPTH 48
 
 // World::hit (world.h:17-20): closest hit over the whole scene in [t_min, t_max].
-template <bool COUNT>
+template <bool COUNT, bool MEDIA = true>
 PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_max, const MediumRng &mr, Hit &out,
                          TraceCounters *counters)
 {
@@ -266,7 +283,7 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
     PrimHit best;
     best.t = 0.f;
     best.n = v3(0.f, 0.f, 0.f);
-    best.u = best.v = 0.f;
+    best.face = 0;
 
     int32_t stack_ref[PT_STACK_DEPTH];
     float stack_t[PT_STACK_DEPTH];
@@ -327,7 +344,7 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
             // hands the unshrunk t_max to both children and keeps the RIGHT record unless left.t < right.t
             // (bvh.h:39-48): among equal t the right-most leaf of ITS tree wins.  The instance table is stored in
             // that leaf order (scene_compile.cpp), hence: a tie goes to the higher index.
-            if (hit_instance(I, o, d, t_min, best_t, mr, h) && (h.t < best_t || idx > best_inst)) {
+            if (hit_instance<MEDIA>(I, o, d, t_min, best_t, mr, h) && (h.t < best_t || idx > best_inst)) {
                 best_t = h.t;
                 best = h;
                 best_inst = idx;
@@ -360,8 +377,24 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
     out.t = best.t;
     out.p = xform_point(fwd, pl);
     out.n = eigen_normalized(xform_vector_transposed(I.inv, best.n));
-    out.u = best.u;
-    out.v = best.v;
+    // rec.u / rec.v: only rect::hit sets them (primitive.h:206-207; a box side is a rect); sphere and
+    // constant_medium leave them as they were (Q11) -- reported as 0
+    out.u = out.v = 0.f;
+    if (!(MEDIA && meta_medium(I.meta))) {
+        const int kind = meta_kind(I.meta);
+        const float *p = I.p;
+        if (kind == B200PT_PRIM_RECT) {
+            rect_uv(meta_plane(I.meta), p[0], p[1], p[2], p[3], lo, ld, best.t, out.u, out.v);
+        } else if (kind == B200PT_PRIM_BOX) {
+            const int f = best.face >> 1;
+            if (f == 0)
+                rect_uv(B200PT_PLANE_XY, p[0], p[1], p[3], p[4], lo, ld, best.t, out.u, out.v);
+            else if (f == 1)
+                rect_uv(B200PT_PLANE_YZ, p[1], p[2], p[4], p[5], lo, ld, best.t, out.u, out.v);
+            else
+                rect_uv(B200PT_PLANE_XZ, p[0], p[2], p[3], p[5], lo, ld, best.t, out.u, out.v);
+        }
+    }
     return true;
 }
 

@@ -59,6 +59,7 @@ struct PtSceneView {
     const float *perlin_ranvec; // 256 x 3
     const int32_t *perlin_perm; // 3 x 256
     int32_t n_nodes, n_inst, n_lights, background;
+    int32_t n_media; // instances wrapped in a constant_medium; 0 selects the kernels compiled without that branch
     PtCamera cam;
 };
 

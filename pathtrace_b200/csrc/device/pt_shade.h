@@ -277,7 +277,7 @@ PT_HD float power_heuristic(float f, float g)
 // ---- one next-event-estimation sample (integrator.h:221-265) --------------------------------------------------
 // W = attenuation * beta at the vertex.  Returns the contribution of light sample k (before the division by
 // light_samples); `traced` tells whether a shadow ray was cast.
-template <bool COUNT>
+template <bool COUNT, bool MEDIA = true>
 PT_HD V3 nee_sample(const PtSceneView &s, const RenderParams &rp, const RngKey &key, int bounce, int k, V3 p, V3 n,
                     int mat_kind, V3 W, TraceCounters *counters)
 {
@@ -301,7 +301,7 @@ PT_HD V3 nee_sample(const PtSceneView &s, const RenderParams &rp, const RngKey &
     mr.xi = -1.f;
     Hit lrec;
     // the shadow ray starts at the un-offset hit point; t is in units of |dir| (integrator.h:235,246) (sic)
-    if (!trace_closest<COUNT>(s, p, dir, 0.001f, PT_FLT_MAX, mr, lrec, counters))
+    if (!trace_closest<COUNT, MEDIA>(s, p, dir, 0.001f, PT_FLT_MAX, mr, lrec, counters))
         return v3(0.f, 0.f, 0.f);
     // whatever is hit first contributes its emission -- `true ||` (integrator.h:250) (sic)
     const b200pt_material &lm = s.mats[meta_material(s.inst[lrec.inst].meta)];

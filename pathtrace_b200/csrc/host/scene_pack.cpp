@@ -73,6 +73,7 @@ pt::PtSceneView PackedScene::host_view(const FlatScene &f) const
     v.n_inst = (int)inst.size();
     v.n_lights = (int)f.lights.size();
     v.background = f.background;
+    v.n_media = n_media;
     v.cam.origin = to_v3(f.camera.origin);
     v.cam.lower_left = to_v3(f.camera.lower_left);
     v.cam.horizontal = to_v3(f.camera.horizontal);
