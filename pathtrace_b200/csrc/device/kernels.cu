@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(kThreads) k_shade(PtSceneView s, RenderParams 
 // adjacent lanes: same origin, nearly the same target -> coherent traversal, and the sum is a fixed-order shuffle
 // reduction; otherwise float atomics.
 template <bool COUNT, bool MEDIA>
-__global__ void __launch_bounds__(kThreads) k_nee(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
+__global__ void __launch_bounds__(kThreads, MEDIA ? 3 : 4) k_nee(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
     TraceCounters tc;
     tc.boxes = tc.prims = 0;

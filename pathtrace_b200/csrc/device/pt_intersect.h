@@ -148,18 +148,83 @@ PT_HD bool hit_prim(uint32_t meta, const float *p, V3 o, V3 d, float t_min, floa
     return hit_box(p, o, d, t_min, t_max, h);
 }
 
-// constant_medium::hit (volume.h:29-93).  xi = the uniform variate of volume.h:70.  xi2 >= 0: a second,
-// independent variate for a medium that the reference BVH holds twice (bvh.h:150-153; both copies are
-// intersected and the nearer event wins, which is the minimum of two free-flight draws).
-PT_HD bool hit_medium(uint32_t meta, const float *p, float density, V3 o, V3 d, float t_min, float t_max, float xi,
-                      float xi2, PrimHit &h)
+// Where a traversal gets the medium variates from.  One Philox call serves two medium slots ({xi, xi2} each), and
+// the last block drawn is kept: a ray that meets the same media again (the usual case: a scene-wide mist) pays for
+// the generator once.
+struct MediumRng {
+    RngKey key;
+    uint32_t stage; // stage word; counter index = medium slot / 2
+    float xi;       // >= 0: explicit variate for every medium (b200pt_trace_batch); < 0: use the Philox stream
+    mutable int32_t cached_block = -1;
+    mutable F4 cached;
+};
+
+// the variates of medium `slot`: xi for volume.h:70, xi2 for the second copy of a BVH-duplicated medium
+PT_HD void medium_variates(const MediumRng &mr, uint32_t slot, bool dup, float &xi, float &xi2)
 {
-    PrimHit rec1, rec2;
-    if (!hit_prim(meta, p, o, d, -PT_FLT_MAX, PT_FLT_MAX, rec1))
-        return false;
-    if (!hit_prim(meta, p, o, d, rec1.t + 0.0001f, PT_FLT_MAX, rec2))
-        return false;
-    float ta = rec1.t, tb = rec2.t;
+    xi2 = -1.f;
+    if (mr.xi >= 0.f) {
+        xi = mr.xi;
+        return;
+    }
+    const int32_t block = (int32_t)(slot >> 1);
+    if (block != mr.cached_block) {
+        mr.cached = rng4(mr.key, mr.stage, (uint32_t)block);
+        mr.cached_block = block;
+    }
+    const bool odd = slot & 1u;
+    xi = odd ? mr.cached.z : mr.cached.x;
+    if (dup)
+        xi2 = odd ? mr.cached.w : mr.cached.y;
+}
+
+// first root of the sphere quadratic inside (t_lo, t_hi), in sphere::hit's order (primitive.h:72-92)
+PT_HD bool sphere_pick(float r1, float r2, float t_lo, float t_hi, float &t)
+{
+    if (r1 < t_hi && r1 > t_lo) {
+        t = r1;
+        return true;
+    }
+    if (r2 < t_hi && r2 > t_lo) {
+        t = r2;
+        return true;
+    }
+    return false;
+}
+
+// constant_medium::hit (volume.h:29-93): boundary->hit over (-inf, inf) gives the entry, boundary->hit from
+// entry + 0.0001 the exit; the event distance is drawn only when the clipped interval is not empty (volume.h:70).
+// A BVH-duplicated medium (bvh.h:150-153) is intersected twice by the reference and the nearer event wins: the
+// minimum of two free-flight draws.
+PT_HD bool hit_medium(uint32_t meta, const float *p, float density, V3 o, V3 d, float t_min, float t_max,
+                      const MediumRng &mr, PrimHit &h)
+{
+    float ta, tb;
+    if (meta_kind(meta) == B200PT_PRIM_SPHERE) {
+        // both calls of sphere::hit evaluate the same two roots
+        V3 center = v3(p[0], p[1], p[2]);
+        V3 oc = o - center;
+        float a = dot(d, d);
+        float b = dot(oc, d);
+        float c = dot(oc, oc) - p[3] * p[3];
+        float discriminant = b * b - a * c;
+        if (!(discriminant > 0))
+            return false;
+        float sq = sqrtf(discriminant);
+        float r1 = (-b - sq) / a, r2 = (-b + sq) / a;
+        if (!sphere_pick(r1, r2, -PT_FLT_MAX, PT_FLT_MAX, ta))
+            return false;
+        if (!sphere_pick(r1, r2, (float)((double)ta + 0.0001), PT_FLT_MAX, tb)) // `rec1.t + 0.0001` is a double sum
+            return false;
+    } else {
+        PrimHit rec1, rec2;
+        if (!hit_prim(meta, p, o, d, -PT_FLT_MAX, PT_FLT_MAX, rec1))
+            return false;
+        if (!hit_prim(meta, p, o, d, (float)((double)rec1.t + 0.0001), PT_FLT_MAX, rec2))
+            return false;
+        ta = rec1.t;
+        tb = rec2.t;
+    }
     if (ta < t_min)
         ta = t_min;
     if (tb > t_max)
@@ -168,6 +233,8 @@ PT_HD bool hit_medium(uint32_t meta, const float *p, float density, V3 o, V3 d, 
         return false;
     if (ta < 0)
         ta = 0;
+    float xi, xi2;
+    medium_variates(mr, meta_medium_slot(meta), meta_dup(meta), xi, xi2);
     float dlen = length(d);
     float distance_inside_boundary = (tb - ta) * dlen;
     float hit_distance = -(1.f / density) * logf(xi);
@@ -183,13 +250,6 @@ PT_HD bool hit_medium(uint32_t meta, const float *p, float density, V3 o, V3 d, 
     }
     return false;
 }
-
-// Where a traversal gets the medium variates from.
-struct MediumRng {
-    RngKey key;
-    uint32_t stage; // stage word; index = medium slot
-    float xi;       // >= 0: explicit variate for every medium (b200pt_trace_batch); < 0: use the Philox stream
-};
 
 struct InstanceData { // one PtInstance in registers
     float inv[12];
@@ -230,14 +290,7 @@ PT_HD bool hit_instance(const InstanceData &I, V3 o, V3 d, float t_min, float t_
     V3 ld = xform_vector(I.inv, d);
     if (!MEDIA || !meta_medium(I.meta))
         return hit_prim(I.meta, I.p, lo, ld, t_min, t_max, h);
-    float xi = mr.xi, xi2 = -1.f;
-    if (xi < 0.f) {
-        F4 r = rng4(mr.key, mr.stage, meta_medium_slot(I.meta));
-        xi = r.x;
-        if (meta_dup(I.meta))
-            xi2 = r.y;
-    }
-    return hit_medium(I.meta, I.p, I.density, lo, ld, t_min, t_max, xi, xi2, h);
+    return hit_medium(I.meta, I.p, I.density, lo, ld, t_min, t_max, mr, h);
 }
 
 // aabb::hit (aabb.h:34-53) of one child half, used as a culling test against [t_min, t_limit] (inclusive).
@@ -272,25 +325,51 @@ struct TraceCounters {
 
 #define PT_STACK_DEPTH 48
 
-// World::hit (world.h:17-20): closest hit over the whole scene in [t_min, t_max].
-template <bool COUNT, bool MEDIA = true>
-PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_max, const MediumRng &mr, Hit &out,
-                         TraceCounters *counters)
-{
-    const V3 inv_d = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-    float best_t = t_max;
-    int best_inst = -1;
+// World::hit (world.h:17-20) as a resumable state machine: init() -> step() until it returns false -> result().
+// One step = descend through inner nodes to the next leaf, test that leaf, pop the next subtree (a "while-while"
+// iteration).  The CPU restatement runs it to completion per ray (trace_closest); the persistent kernels keep one
+// in flight per lane and hand a lane a new ray as soon as its traversal ends (kernels.cu persistent_trace).
+struct Traversal {
+    V3 o, d, inv_d;
+    float t_min, best_t;
+    int32_t best_inst;
     PrimHit best;
-    best.t = 0.f;
-    best.n = v3(0.f, 0.f, 0.f);
-    best.face = 0;
-
+    int32_t cur; // node to visit next: >= 0 inner node, < 0 leaf (~instance)
+    int32_t sp;
     int32_t stack_ref[PT_STACK_DEPTH];
     float stack_t[PT_STACK_DEPTH];
-    int sp = 0;
-    int32_t cur = 0; // root node
-    bool have = true;
-    while (have) {
+
+    PT_HD void init(V3 origin, V3 dir, float tmin, float tmax)
+    {
+        o = origin;
+        d = dir;
+        inv_d = v3(1.0f / dir.x, 1.0f / dir.y, 1.0f / dir.z);
+        t_min = tmin;
+        best_t = tmax;
+        best_inst = -1;
+        best.t = 0.f;
+        best.n = v3(0.f, 0.f, 0.f);
+        best.face = 0;
+        cur = 0; // root
+        sp = 0;
+    }
+
+    PT_HD bool pop()
+    {
+        const float lim = cull_limit(best_t);
+        while (sp > 0) {
+            sp--;
+            if (stack_t[sp] <= lim) {
+                cur = stack_ref[sp];
+                return true;
+            }
+        }
+        return false;
+    }
+
+    // returns false when the traversal is complete
+    template <bool COUNT, bool MEDIA> PT_HD bool step(const PtSceneView &s, const MediumRng &mr, TraceCounters *counters)
+    {
         while (cur >= 0) {
             const PtNode *node = s.nodes + cur;
 #if defined(__CUDA_ARCH__)
@@ -326,76 +405,79 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
                 cur = ref0;
             } else if (h1) {
                 cur = ref1;
-            } else {
-                have = false;
-                break;
+            } else if (!pop()) {
+                return false;
             }
         }
-        if (have) {
-            // leaf: one instance
-            int idx = ~cur;
-            InstanceData I;
-            load_instance(s.inst, idx, I);
-            PrimHit h;
-            if (COUNT)
-                counters->prims += 1;
-            // Every primitive test is inclusive at its upper bound or never ties (rect: `t > t1` rejects,
-            // primitive.h:196; sphere: strict), so a surface at exactly best_t is reported again.  The reference
-            // hands the unshrunk t_max to both children and keeps the RIGHT record unless left.t < right.t
-            // (bvh.h:39-48): among equal t the right-most leaf of ITS tree wins.  The instance table is stored in
-            // that leaf order (scene_compile.cpp), hence: a tie goes to the higher index.
-            if (hit_instance<MEDIA>(I, o, d, t_min, best_t, mr, h) && (h.t < best_t || idx > best_inst)) {
-                best_t = h.t;
-                best = h;
-                best_inst = idx;
+        // leaf: one instance
+        const int idx = ~cur;
+        InstanceData I;
+        load_instance(s.inst, idx, I);
+        PrimHit h;
+        if (COUNT)
+            counters->prims += 1;
+        // Every primitive test is inclusive at its upper bound or never ties (rect: `t > t1` rejects,
+        // primitive.h:196; sphere: strict), so a surface at exactly best_t is reported again.  The reference hands
+        // the unshrunk t_max to both children and keeps the RIGHT record unless left.t < right.t (bvh.h:39-48):
+        // among equal t the right-most leaf of ITS tree wins.  The instance table is stored in that leaf order
+        // (scene_compile.cpp), hence: a tie goes to the higher index.
+        if (hit_instance<MEDIA>(I, o, d, t_min, best_t, mr, h) && (h.t < best_t || idx > best_inst)) {
+            best_t = h.t;
+            best = h;
+            best_inst = idx;
+        }
+        return pop();
+    }
+
+    // instance::hit epilogue (primitive.h:302-305): p and normal back to world space, rec.u / rec.v
+    template <bool MEDIA> PT_HD bool result(const PtSceneView &s, Hit &out) const
+    {
+        if (best_inst < 0) {
+            out.inst = -1;
+            return false;
+        }
+        InstanceData I;
+        load_instance(s.inst, best_inst, I);
+        V3 lo = xform_point(I.inv, o);
+        V3 ld = xform_vector(I.inv, d);
+        V3 pl = lo + best.t * ld;
+        const float *fwd = s.fwd[best_inst].m;
+        out.inst = best_inst;
+        out.t = best.t;
+        out.p = xform_point(fwd, pl);
+        out.n = eigen_normalized(xform_vector_transposed(I.inv, best.n));
+        // rec.u / rec.v: only rect::hit sets them (primitive.h:206-207; a box side is a rect); sphere and
+        // constant_medium leave them as they were (Q11) -- reported as 0
+        out.u = out.v = 0.f;
+        if (!(MEDIA && meta_medium(I.meta))) {
+            const int kind = meta_kind(I.meta);
+            const float *p = I.p;
+            if (kind == B200PT_PRIM_RECT) {
+                rect_uv(meta_plane(I.meta), p[0], p[1], p[2], p[3], lo, ld, best.t, out.u, out.v);
+            } else if (kind == B200PT_PRIM_BOX) {
+                const int f = best.face >> 1;
+                if (f == 0)
+                    rect_uv(B200PT_PLANE_XY, p[0], p[1], p[3], p[4], lo, ld, best.t, out.u, out.v);
+                else if (f == 1)
+                    rect_uv(B200PT_PLANE_YZ, p[1], p[2], p[4], p[5], lo, ld, best.t, out.u, out.v);
+                else
+                    rect_uv(B200PT_PLANE_XZ, p[0], p[2], p[3], p[5], lo, ld, best.t, out.u, out.v);
             }
         }
-        // pop
-        have = false;
-        const float lim = cull_limit(best_t);
-        while (sp > 0) {
-            sp--;
-            if (stack_t[sp] <= lim) {
-                cur = stack_ref[sp];
-                have = true;
-                break;
-            }
-        }
+        return true;
     }
-    if (best_inst < 0) {
-        out.inst = -1;
-        return false;
+};
+
+// World::hit (world.h:17-20): closest hit over the whole scene in [t_min, t_max], one ray run to completion.
+template <bool COUNT, bool MEDIA = true>
+PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_max, const MediumRng &mr, Hit &out,
+                         TraceCounters *counters)
+{
+    Traversal T;
+    T.init(o, d, t_min, t_max);
+    while (T.template step<COUNT, MEDIA>(s, mr, counters)) {
     }
-    // instance::hit epilogue (primitive.h:302-305): p and normal back to world space
-    InstanceData I;
-    load_instance(s.inst, best_inst, I);
-    V3 lo = xform_point(I.inv, o);
-    V3 ld = xform_vector(I.inv, d);
-    V3 pl = lo + best.t * ld;
-    const float *fwd = s.fwd[best_inst].m;
-    out.inst = best_inst;
-    out.t = best.t;
-    out.p = xform_point(fwd, pl);
-    out.n = eigen_normalized(xform_vector_transposed(I.inv, best.n));
-    // rec.u / rec.v: only rect::hit sets them (primitive.h:206-207; a box side is a rect); sphere and
-    // constant_medium leave them as they were (Q11) -- reported as 0
-    out.u = out.v = 0.f;
-    if (!(MEDIA && meta_medium(I.meta))) {
-        const int kind = meta_kind(I.meta);
-        const float *p = I.p;
-        if (kind == B200PT_PRIM_RECT) {
-            rect_uv(meta_plane(I.meta), p[0], p[1], p[2], p[3], lo, ld, best.t, out.u, out.v);
-        } else if (kind == B200PT_PRIM_BOX) {
-            const int f = best.face >> 1;
-            if (f == 0)
-                rect_uv(B200PT_PLANE_XY, p[0], p[1], p[3], p[4], lo, ld, best.t, out.u, out.v);
-            else if (f == 1)
-                rect_uv(B200PT_PLANE_YZ, p[1], p[2], p[4], p[5], lo, ld, best.t, out.u, out.v);
-            else
-                rect_uv(B200PT_PLANE_XZ, p[0], p[2], p[3], p[5], lo, ld, best.t, out.u, out.v);
-        }
-    }
-    return true;
+    return T.template result<MEDIA>(s, out);
 }
 
 } // namespace pt

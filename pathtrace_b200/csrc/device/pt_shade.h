@@ -275,18 +275,25 @@ PT_HD float power_heuristic(float f, float g)
 }
 
 // ---- one next-event-estimation sample (integrator.h:221-265) --------------------------------------------------
-// W = attenuation * beta at the vertex.  Returns the contribution of light sample k (before the division by
-// light_samples); `traced` tells whether a shadow ray was cast.
-template <bool COUNT, bool MEDIA = true>
-PT_HD V3 nee_sample(const PtSceneView &s, const RenderParams &rp, const RngKey &key, int bounce, int k, V3 p, V3 n,
-                    int mat_kind, V3 W, TraceCounters *counters)
+// Split around the shadow ray so that a kernel can keep the ray in flight between the two halves:
+//   nee_prepare  light pick, light sample, pdfs, MIS weight -> ray direction + everything but the emission
+//   nee_finish   emission of whatever the shadow ray hit first -> the sample's contribution
+// W = attenuation * beta at the vertex.  The contribution is before the division by light_samples.
+struct NeeSample {
+    V3 dir;  // shadow ray direction, un-normalised: the light point minus p (integrator.h:235)
+    V3 coef; // attenuation * beta * weight_l / light_pdf_l * max(cos_l, 0)
+    float pick_pdf;
+};
+
+PT_HD void nee_prepare(const PtSceneView &s, const RngKey &key, int bounce, int k, V3 p, V3 n, int mat_kind, V3 W,
+                       NeeSample &out)
 {
     F4 r = rng4(key, stage_word(bounce, RNG_NEE, k), 0);
     int li = (int)(r.x * s.n_lights); // World::get_random_light (world.h:31-35)
     if (li >= s.n_lights)
         li = s.n_lights - 1;
     const int light_inst = s.lights[li];
-    const float pick_pdf = (float)s.n_lights; // (sic) integrator.h:224
+    out.pick_pdf = (float)s.n_lights; // (sic) integrator.h:224
     InstanceData L;
     load_instance(s.inst, light_inst, L);
     V3 dir = light_random(L, s.fwd[light_inst].m, p, r.y, r.z);
@@ -294,27 +301,48 @@ PT_HD V3 nee_sample(const PtSceneView &s, const RenderParams &rp, const RngKey &
     float light_pdf_l = light_pdf_value(L, p, dir);
     float scatter_pdf_l = mat_value(mat_kind, n, dir);
     float weight_l = power_heuristic(light_pdf_l, scatter_pdf_l);
-
-    MediumRng mr;
-    mr.key = key;
-    mr.stage = stage_word(bounce, RNG_NEE_MEDIUM, k);
-    mr.xi = -1.f;
-    Hit lrec;
-    // the shadow ray starts at the un-offset hit point; t is in units of |dir| (integrator.h:235,246) (sic)
-    if (!trace_closest<COUNT, MEDIA>(s, p, dir, 0.001f, PT_FLT_MAX, mr, lrec, counters))
-        return v3(0.f, 0.f, 0.f);
-    // whatever is hit first contributes its emission -- `true ||` (integrator.h:250) (sic)
-    const b200pt_material &lm = s.mats[meta_material(s.inst[lrec.inst].meta)];
-    V3 light_emission = mat_emitted(s, lm, dir, lrec.n, lrec.p);
     float dropoff = fmaxf(cos_l, 0.0f);
     V3 c = W * weight_l;
     c = c / light_pdf_l;
     c = c * dropoff;
-    c = c * light_emission;
-    c = c / pick_pdf;
+    out.dir = dir;
+    out.coef = c;
+}
+
+// lrec: the closest hit of the shadow ray; it starts at the un-offset hit point and t is in units of |dir|
+// (integrator.h:235,246) (sic).  Whatever is hit first contributes its emission -- `true ||` (integrator.h:250) (sic)
+PT_HD V3 nee_finish(const PtSceneView &s, const NeeSample &ns, bool hit, const Hit &lrec)
+{
+    if (!hit)
+        return v3(0.f, 0.f, 0.f);
+    const b200pt_material &lm = s.mats[meta_material(s.inst[lrec.inst].meta)];
+    V3 light_emission = mat_emitted(s, lm, ns.dir, lrec.n, lrec.p);
+    V3 c = ns.coef * light_emission;
+    c = c / ns.pick_pdf;
     if (is_nan(c))
         return v3(0.f, 0.f, 0.f);
     return c;
+}
+
+PT_HD MediumRng nee_medium_rng(const RngKey &key, int bounce, int k)
+{
+    MediumRng mr;
+    mr.key = key;
+    mr.stage = stage_word(bounce, RNG_NEE_MEDIUM, k);
+    mr.xi = -1.f;
+    return mr;
+}
+
+template <bool COUNT, bool MEDIA = true>
+PT_HD V3 nee_sample(const PtSceneView &s, const RenderParams &rp, const RngKey &key, int bounce, int k, V3 p, V3 n,
+                    int mat_kind, V3 W, TraceCounters *counters)
+{
+    NeeSample ns;
+    nee_prepare(s, key, bounce, k, p, n, mat_kind, W, ns);
+    MediumRng mr = nee_medium_rng(key, bounce, k);
+    Hit lrec;
+    bool hit = trace_closest<COUNT, MEDIA>(s, p, ns.dir, 0.001f, PT_FLT_MAX, mr, lrec, counters);
+    return nee_finish(s, ns, hit, lrec);
 }
 
 // ---- the vertex: emission, NEE request, scattering, Russian roulette, throughput (integrator.h:193-323) ------
