@@ -461,8 +461,12 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         const long long target_slots = 8ll << 20;
         int bs = c.batch_samples > 0 ? c.batch_samples : (int)std::max<long long>(1, target_slots / npix);
         bs = std::min(bs, c.samples);
-        while ((long long)bs * npix > (1ll << 30) && bs > 1)
+        // slots (and slots x light_samples, the NEE index space) are 32-bit indices
+        const long long per_slot = c.integrator == B200PT_INTEGRATOR_INEEPT && c.light_samples > 1 ? c.light_samples : 1;
+        while ((long long)bs * npix * per_slot > (1ll << 30) && bs > 1)
             bs--;
+        if ((long long)bs * npix * per_slot >= (1ll << 31))
+            throw std::runtime_error("config: film x light_samples exceeds the 32-bit index space of one wavefront batch");
         r->batch_samples = bs;
         r->batches_total = (c.samples + bs - 1) / bs;
         const size_t cap = (size_t)bs * (size_t)npix;
@@ -482,6 +486,21 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         pt::Wavefront &wf = r->wf;
         wf.npix = (int32_t)npix;
         wf.capacity = (int32_t)cap;
+        {
+            // divide-by-npix constants (Granlund & Montgomery): m = ceil(2^(31+l) / d), l = ceil(log2 d)
+            const uint32_t d = (uint32_t)npix;
+            if (d == 1) {
+                wf.npix_mul = 0;
+                wf.npix_shr = 0;
+            } else {
+                uint32_t l = 0;
+                while ((1ull << l) < d)
+                    l++;
+                const unsigned long long pw = 1ull << (31 + l);
+                wf.npix_mul = (uint32_t)((pw + d - 1) / d);
+                wf.npix_shr = l - 1;
+            }
+        }
         wf.ray_o = render_alloc<float4>(*r, cap);
         wf.ray_d = render_alloc<float4>(*r, cap);
         wf.beta = render_alloc<float4>(*r, cap);

@@ -79,7 +79,9 @@ __device__ __forceinline__ RngKey make_key(const RenderParams &rp, const Wavefro
     RngKey k;
     k.seed_lo = rp.seed_lo;
     k.seed_hi = rp.seed_hi;
-    int s_local = slot / wf.npix;
+    // slot / npix by multiply-high with a host-computed reciprocal (exact for slot < 2^31): an integer division is
+    // ~20 instructions and every kernel keys its random numbers through here
+    int s_local = wf.npix_mul ? (int)(__umulhi((uint32_t)slot, wf.npix_mul) >> wf.npix_shr) : slot;
     k.pixel = (uint32_t)(slot - s_local * wf.npix);
     k.sample = (uint32_t)(sample_base + s_local);
     return k;
@@ -233,23 +235,35 @@ __global__ void __launch_bounds__(kThreads) k_shade(PtSceneView s, RenderParams 
 // One thread per (vertex, light sample).  With light_samples a power of two <= 32 the samples of one vertex sit in
 // adjacent lanes: same origin, nearly the same target -> coherent traversal, and the sum is a fixed-order shuffle
 // reduction; otherwise float atomics.
+#ifndef PT_NEE_MEDIA_MINB
+#define PT_NEE_MEDIA_MINB 3
+#endif
 template <bool COUNT, bool MEDIA>
-__global__ void __launch_bounds__(kThreads, MEDIA ? 3 : 4) k_nee(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
+__global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
     TraceCounters tc;
     tc.boxes = tc.prims = 0;
     unsigned long long nrays = 0;
     const long long sample_base = wf.ctl->sample_base;
     const int L = rp.light_samples;
-    const long long n = (long long)wf.counters[bounce * CNT_ROW + CNT_NEE] * L;
+    // capacity * light_samples < 2^31 is guaranteed by b200pt_render_start (it shrinks the batch otherwise)
+    const unsigned n = (unsigned)wf.counters[bounce * CNT_ROW + CNT_NEE] * (unsigned)L;
     const bool pow2 = (L & (L - 1)) == 0 && L <= 32;
+    const int shift = __ffs(L) - 1;
     const float inv_L_div = (float)L;
-    for (long long base = (long long)blockIdx.x * kThreads; base < n; base += (long long)gridDim.x * kThreads) {
-        const long long e = base + threadIdx.x;
+    for (unsigned base = blockIdx.x * kThreads; base < n; base += gridDim.x * kThreads) {
+        const unsigned e = base + threadIdx.x;
         V3 c = v3(0.f, 0.f, 0.f);
         int slot = -1;
         if (e < n) {
-            int q = (int)(e / L), k = (int)(e - (long long)q * L);
+            int q, k;
+            if (pow2) {
+                q = (int)(e >> shift);
+                k = (int)(e & (unsigned)(L - 1));
+            } else {
+                q = (int)(e / (unsigned)L);
+                k = (int)(e - (unsigned)q * (unsigned)L);
+            }
             slot = wf.q_nee[q];
             float4 hp = wf.hit_p[slot], hn = wf.hit_n[slot], w = wf.nee_w[slot];
             RngKey key = make_key(rp, wf, slot, sample_base);

@@ -46,7 +46,15 @@ PT_HD float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 PT_HD V3 cross(V3 a, V3 b) { return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 PT_HD float length(V3 a) { return sqrtf(a.x * a.x + a.y * a.y + a.z * a.z); }
 PT_HD float squared_length(V3 a) { return a.x * a.x + a.y * a.y + a.z * a.z; }
-PT_HD V3 unit_vector(V3 a) { return a / length(a); } // vec3.h:196-199
+// a / t as one reciprocal and three products.  The reference's vec3 divides component-wise (vec3.h:124-127); the
+// hit routine keeps that (operator/) because its records are compared bit for bit, the shading code -- compared
+// statistically -- uses this form: an IEEE division costs ~10 instructions on the GPU.
+PT_HD V3 div_fast(V3 a, float t)
+{
+    float k = 1.0f / t;
+    return v3(a.x * k, a.y * k, a.z * k);
+}
+PT_HD V3 unit_vector(V3 a) { return div_fast(a, length(a)); } // vec3.h:196-199
 // Eigen 3.2.10 Vector3f::normalized(): v / sqrt(x*x + (y*y + z*z)) -- its 3-element sum splits 1 + 2
 // (Core/Redux.h redux_novec_unroller).  Used where the reference normalises through Eigen (transform3.h:60-63).
 PT_HD V3 eigen_normalized(V3 a)

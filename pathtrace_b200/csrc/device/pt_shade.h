@@ -96,14 +96,14 @@ PT_HD bool mat_scatter(const PtSceneView &s, const b200pt_material &m, V3 ray_di
             V3 value;
             float alpha;
             tex_eval(s, m.texture, p, value, alpha);
-            attenuation = value / PT_PI_F;
+            attenuation = value * (1.0f / PT_PI_F);
         } else {
             attenuation = v3(0.f, 0.f, 0.f);
         }
         return true;
     }
     case B200PT_MAT_METAL: // a cosine lobe with constant albedo, no facing test (material.h:90-98) (sic)
-        attenuation = v3(m.color[0], m.color[1], m.color[2]) / PT_PI_F;
+        attenuation = v3(m.color[0], m.color[1], m.color[2]) * (1.0f / PT_PI_F);
         return true;
     case B200PT_MAT_DIELECTRIC:
         attenuation = v3(1.f, 1.f, 1.f);
@@ -126,7 +126,7 @@ PT_HD float mat_value(int kind, V3 n, V3 direction)
     if (kind == B200PT_MAT_LAMBERTIAN || kind == B200PT_MAT_METAL) {
         // cosine_pdf::value (pdf.h:18-28); uvw.w() = unit_vector(n)
         float cosine = dot(unit_vector(direction), unit_vector(n));
-        return cosine > 0 ? cosine / PT_PI_F : 0.f;
+        return cosine > 0 ? cosine * (1.0f / PT_PI_F) : 0.f;
     }
     if (kind == B200PT_MAT_ISOTROPIC)
         return (float)(1 / (4 * 3.14159265358979323846)); // random_pdf::value (pdf.h:41-44)
@@ -303,7 +303,7 @@ PT_HD void nee_prepare(const PtSceneView &s, const RngKey &key, int bounce, int 
     float weight_l = power_heuristic(light_pdf_l, scatter_pdf_l);
     float dropoff = fmaxf(cos_l, 0.0f);
     V3 c = W * weight_l;
-    c = c / light_pdf_l;
+    c = div_fast(c, light_pdf_l);
     c = c * dropoff;
     out.dir = dir;
     out.coef = c;
@@ -318,7 +318,7 @@ PT_HD V3 nee_finish(const PtSceneView &s, const NeeSample &ns, bool hit, const H
     const b200pt_material &lm = s.mats[meta_material(s.inst[lrec.inst].meta)];
     V3 light_emission = mat_emitted(s, lm, ns.dir, lrec.n, lrec.p);
     V3 c = ns.coef * light_emission;
-    c = c / ns.pick_pdf;
+    c = div_fast(c, ns.pick_pdf);
     if (is_nan(c))
         return v3(0.f, 0.f, 0.f);
     return c;

@@ -46,6 +46,7 @@ struct Wavefront {
     unsigned long long *trace_counts; // profile == 2: {ext rays, boxes, prims, nee rays, boxes, prims}
     int32_t npix;
     int32_t capacity; // slots
+    uint32_t npix_mul, npix_shr; // slot / npix == umulhi(slot, npix_mul) >> npix_shr (npix_mul == 0: npix == 1)
 };
 
 struct Film {
