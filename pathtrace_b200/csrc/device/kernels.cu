@@ -137,17 +137,23 @@ __global__ void __launch_bounds__(kThreads) k_extend(PtSceneView s, RenderParams
         const int i = base + threadIdx.x;
         unsigned mask = 0;
         int slot = 0;
-        if (i < n) {
+        const bool live = i < n;
+        Traversal T;
+        MediumRng mr;
+        mr.xi = -1.f;
+        if (live) {
             slot = q_in ? q_in[i] : i;
             float4 ro = wf.ray_o[slot], rd = wf.ray_d[slot];
-            MediumRng mr;
             mr.key = make_key(rp, wf, slot, sample_base);
             mr.stage = stage_word(bounce, RNG_EXT_MEDIUM, 0);
-            mr.xi = -1.f;
+            T.init(xyz(ro), xyz(rd), 0.001f, PT_FLT_MAX);
+            nrays++;
+        }
+        T.template run_warp<COUNT, MEDIA>(s, live, mr, &tc); // all 32 lanes take part in the votes
+        if (live) {
             Hit h;
             int kind = SK_MISS;
-            nrays++;
-            if (trace_closest<COUNT, MEDIA>(s, xyz(ro), xyz(rd), 0.001f, PT_FLT_MAX, mr, h, &tc)) {
+            if (T.template result<MEDIA>(s, h)) {
                 wf.hit_p[slot] = f4(h.p, __int_as_float(h.inst));
                 wf.hit_n[slot] = f4(h.n, h.t);
                 kind = shade_kind_of(s.mats[meta_material(s.inst[h.inst].meta)].kind);
@@ -255,6 +261,10 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
         const unsigned e = base + threadIdx.x;
         V3 c = v3(0.f, 0.f, 0.f);
         int slot = -1;
+        Traversal T;
+        MediumRng mr;
+        mr.xi = -1.f;
+        NeeSample ns;
         if (e < n) {
             int q, k;
             if (pow2) {
@@ -268,7 +278,15 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
             float4 hp = wf.hit_p[slot], hn = wf.hit_n[slot], w = wf.nee_w[slot];
             RngKey key = make_key(rp, wf, slot, sample_base);
             nrays++;
-            c = nee_sample<COUNT, MEDIA>(s, rp, key, bounce, k, xyz(hp), xyz(hn), __float_as_int(w.w), xyz(w), &tc);
+            nee_prepare(s, key, bounce, k, xyz(hp), xyz(hn), __float_as_int(w.w), xyz(w), ns);
+            mr = nee_medium_rng(key, bounce, k);
+            T.init(xyz(hp), ns.dir, 0.001f, PT_FLT_MAX);
+        }
+        T.template run_warp<COUNT, MEDIA>(s, slot >= 0, mr, &tc); // all 32 lanes take part in the votes
+        if (slot >= 0) {
+            Hit lrec;
+            const bool hit = T.template result<MEDIA>(s, lrec);
+            c = nee_finish(s, ns, hit, lrec);
         }
         if (pow2) {
             // lanes [g*L, (g+1)*L) hold one vertex (kThreads and 32 are multiples of L)
@@ -370,20 +388,30 @@ __global__ void __launch_bounds__(kThreads) k_trace_batch(PtSceneView s, const f
                                                           b200pt_hit *__restrict__ hits, unsigned long long *counts)
 {
     unsigned long long boxes = 0, prims = 0, nhit = 0;
-    for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (size_t)gridDim.x * kThreads) {
-        const float4 *r4 = reinterpret_cast<const float4 *>(rays + i * 8);
-        float4 a = __ldg(r4), b = __ldg(r4 + 1);
+    for (size_t base = (size_t)blockIdx.x * kThreads; base < n; base += (size_t)gridDim.x * kThreads) {
+        const size_t i = base + threadIdx.x;
+        const bool live = i < n;
+        Traversal T;
         MediumRng mr;
-        mr.key.seed_lo = 0;
-        mr.key.seed_hi = 0;
-        mr.key.pixel = (uint32_t)(i & 0xffffffffull);
-        mr.key.sample = (uint32_t)(i >> 32);
-        mr.stage = stage_word(0, RNG_BATCH_MEDIUM, 0);
-        mr.xi = medium_xi ? medium_xi[i] : -1.f;
-        Hit h;
+        mr.xi = -1.f;
         TraceCounters tc;
         tc.boxes = tc.prims = 0;
-        bool ok = trace_closest<COUNT, MEDIA>(s, v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), b.z, b.w, mr, h, &tc);
+        if (live) {
+            const float4 *r4 = reinterpret_cast<const float4 *>(rays + i * 8);
+            float4 a = __ldg(r4), b = __ldg(r4 + 1);
+            mr.key.seed_lo = 0;
+            mr.key.seed_hi = 0;
+            mr.key.pixel = (uint32_t)(i & 0xffffffffull);
+            mr.key.sample = (uint32_t)(i >> 32);
+            mr.stage = stage_word(0, RNG_BATCH_MEDIUM, 0);
+            mr.xi = medium_xi ? medium_xi[i] : -1.f;
+            T.init(v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), b.z, b.w);
+        }
+        T.template run_warp<COUNT, MEDIA>(s, live, mr, &tc); // all 32 lanes take part in the votes
+        if (!live)
+            continue;
+        Hit h;
+        bool ok = T.template result<MEDIA>(s, h);
         if (COUNT) {
             boxes += tc.boxes;
             prims += tc.prims;

@@ -325,10 +325,9 @@ struct TraceCounters {
 
 #define PT_STACK_DEPTH 48
 
-// World::hit (world.h:17-20) as a resumable state machine: init() -> step() until it returns false -> result().
-// One step = descend through inner nodes to the next leaf, test that leaf, pop the next subtree (a "while-while"
-// iteration).  The CPU restatement runs it to completion per ray (trace_closest); the persistent kernels keep one
-// in flight per lane and hand a lane a new ray as soon as its traversal ends (kernels.cu persistent_trace).
+// World::hit (world.h:17-20) as a resumable state machine: init() -> steps until one returns false -> result().
+// A step visits one inner node (node_step) or tests one leaf (leaf_step).  The CPU restatement runs a ray to
+// completion (run / trace_closest); the kernels run 32 rays per warp and vote on the kind of step (run_warp).
 struct Traversal {
     V3 o, d, inv_d;
     float t_min, best_t;
@@ -367,49 +366,57 @@ struct Traversal {
         return false;
     }
 
-    // returns false when the traversal is complete
-    template <bool COUNT, bool MEDIA> PT_HD bool step(const PtSceneView &s, const MediumRng &mr, TraceCounters *counters)
+    // One inner node (cur >= 0): slab tests of both children, descend into the nearer one, push the other.
+    // Returns false when the traversal is complete.
+    template <bool COUNT> PT_HD bool node_step(const PtSceneView &s, TraceCounters *counters)
     {
-        while (cur >= 0) {
-            const PtNode *node = s.nodes + cur;
+        const PtNode *node = s.nodes + cur;
 #if defined(__CUDA_ARCH__)
-            const float4 *q = reinterpret_cast<const float4 *>(node);
-            float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), e = __ldg(q + 3);
-            float lo0[3] = {a.x, a.y, a.z}, hi0[3] = {b.x, b.y, b.z}, lo1[3] = {c.x, c.y, c.z}, hi1[3] = {e.x, e.y, e.z};
-            int32_t ref0 = __float_as_int(a.w), ref1 = __float_as_int(c.w);
+        const float4 *q = reinterpret_cast<const float4 *>(node);
+        float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), e = __ldg(q + 3);
+        float lo0[3] = {a.x, a.y, a.z}, hi0[3] = {b.x, b.y, b.z}, lo1[3] = {c.x, c.y, c.z}, hi1[3] = {e.x, e.y, e.z};
+        int32_t ref0 = __float_as_int(a.w), ref1 = __float_as_int(c.w);
 #else
-            const float *lo0 = node->lo0, *hi0 = node->hi0, *lo1 = node->lo1, *hi1 = node->hi1;
-            int32_t ref0 = node->ref0, ref1 = node->ref1;
+        const float *lo0 = node->lo0, *hi0 = node->hi0, *lo1 = node->lo1, *hi1 = node->hi1;
+        int32_t ref0 = node->ref0, ref1 = node->ref1;
 #endif
-            float e0, e1;
-            const float lim = cull_limit(best_t);
-            bool h0 = hit_aabb(lo0, hi0, o, inv_d, t_min, lim, e0);
-            bool h1 = hit_aabb(lo1, hi1, o, inv_d, t_min, lim, e1);
-            if (COUNT)
-                counters->boxes += 2;
-            if (h0 && h1) {
-                int32_t near_ref = ref0, far_ref = ref1;
-                float far_t = e1;
-                if (e1 < e0) {
-                    near_ref = ref1;
-                    far_ref = ref0;
-                    far_t = e0;
-                }
-                if (sp < PT_STACK_DEPTH) {
-                    stack_ref[sp] = far_ref;
-                    stack_t[sp] = far_t;
-                    sp++;
-                }
-                cur = near_ref;
-            } else if (h0) {
-                cur = ref0;
-            } else if (h1) {
-                cur = ref1;
-            } else if (!pop()) {
-                return false;
+        float e0, e1;
+        const float lim = cull_limit(best_t);
+        bool h0 = hit_aabb(lo0, hi0, o, inv_d, t_min, lim, e0);
+        bool h1 = hit_aabb(lo1, hi1, o, inv_d, t_min, lim, e1);
+        if (COUNT)
+            counters->boxes += 2;
+        if (h0 && h1) {
+            int32_t near_ref = ref0, far_ref = ref1;
+            float far_t = e1;
+            if (e1 < e0) {
+                near_ref = ref1;
+                far_ref = ref0;
+                far_t = e0;
             }
+            if (sp < PT_STACK_DEPTH) {
+                stack_ref[sp] = far_ref;
+                stack_t[sp] = far_t;
+                sp++;
+            }
+            cur = near_ref;
+            return true;
         }
-        // leaf: one instance
+        if (h0) {
+            cur = ref0;
+            return true;
+        }
+        if (h1) {
+            cur = ref1;
+            return true;
+        }
+        return pop();
+    }
+
+    // One leaf (cur < 0): the instance ~cur.  Returns false when the traversal is complete.
+    template <bool COUNT, bool MEDIA>
+    PT_HD bool leaf_step(const PtSceneView &s, const MediumRng &mr, TraceCounters *counters)
+    {
         const int idx = ~cur;
         InstanceData I;
         load_instance(s.inst, idx, I);
@@ -428,6 +435,41 @@ struct Traversal {
         }
         return pop();
     }
+
+    // one ray run to completion (CPU restatement, and any caller without a warp to vote with)
+    template <bool COUNT, bool MEDIA> PT_HD void run(const PtSceneView &s, const MediumRng &mr, TraceCounters *counters)
+    {
+        bool more = true;
+        while (more)
+            more = cur >= 0 ? node_step<COUNT>(s, counters) : leaf_step<COUNT, MEDIA>(s, mr, counters);
+    }
+
+#if defined(__CUDACC__)
+    // The same state machine driven by the whole warp: every round the warp votes and runs ONE kind of step --
+    // the one more of its lanes are waiting for.  Rays need different numbers of node visits between two leaves;
+    // letting each lane loop on its own (while-while) left 14 of 32 lanes busy in the node loop and 6 in the leaf
+    // code on the 8192-instance scene (ncu, profiles/r1b_*).  With the vote the step that runs always has at least
+    // half of the unfinished lanes in it, and the code of the other kind is not interleaved with it.
+    // Must be called by all 32 lanes (`active` = this lane has a ray).  Per ray the sequence of steps is the one
+    // run() takes, so the result is identical.
+    template <bool COUNT, bool MEDIA>
+    __device__ __forceinline__ void run_warp(const PtSceneView &s, bool active, const MediumRng &mr, TraceCounters *counters)
+    {
+        while (true) {
+            const unsigned m_act = __ballot_sync(0xffffffffu, active);
+            if (!m_act)
+                break;
+            const unsigned m_in = __ballot_sync(0xffffffffu, active && cur >= 0);
+            if (2 * __popc(m_in) >= __popc(m_act)) {
+                if (active && cur >= 0)
+                    active = node_step<COUNT>(s, counters);
+            } else {
+                if (active && cur < 0)
+                    active = leaf_step<COUNT, MEDIA>(s, mr, counters);
+            }
+        }
+    }
+#endif
 
     // instance::hit epilogue (primitive.h:302-305): p and normal back to world space, rec.u / rec.v
     template <bool MEDIA> PT_HD bool result(const PtSceneView &s, Hit &out) const
@@ -475,8 +517,7 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
 {
     Traversal T;
     T.init(o, d, t_min, t_max);
-    while (T.template step<COUNT, MEDIA>(s, mr, counters)) {
-    }
+    T.template run<COUNT, MEDIA>(s, mr, counters);
     return T.template result<MEDIA>(s, out);
 }
 
