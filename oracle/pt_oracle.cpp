@@ -147,8 +147,10 @@ void *pt_oracle_scene_create(const char *scene_json, int film_w, int film_h)
 
 void pt_oracle_scene_destroy(void *scene) { delete (OracleScene *)scene; }
 
-// World::hit for n rays; same contract as b200pt_trace_batch
-int pt_oracle_trace(void *scene, const float *rays, size_t n, const float *medium_xi, b200pt_hit *hits)
+// World::hit for n rays; same contract as b200pt_trace_batch.  shadow != 0: the NEE shadow query instead
+// (trace_shadow: a record only when the first thing met is an emitter), and emitter_flags[i] (optional, n_inst
+// bytes) reports which instances are emitters -- tests check it against World::hit filtered by those flags.
+static int trace_impl(void *scene, const float *rays, size_t n, const float *medium_xi, b200pt_hit *hits, int shadow)
 {
     OracleScene *sc = (OracleScene *)scene;
     for (size_t i = 0; i < n; i++) {
@@ -160,7 +162,8 @@ int pt_oracle_trace(void *scene, const float *rays, size_t n, const float *mediu
         mr.stage = stage_word(0, RNG_BATCH_MEDIUM, 0);
         mr.xi = medium_xi ? medium_xi[i] : -1.f;
         Hit h;
-        bool ok = trace_closest<false>(sc->view, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7], mr, h, nullptr);
+        bool ok = shadow ? trace_shadow<false>(sc->view, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7], mr, h, nullptr)
+                         : trace_closest<false>(sc->view, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7], mr, h, nullptr);
         b200pt_hit &o = hits[i];
         memset(&o, 0, sizeof(o));
         o.instance = -1;
@@ -174,6 +177,26 @@ int pt_oracle_trace(void *scene, const float *rays, size_t n, const float *mediu
         }
     }
     return 0;
+}
+
+int pt_oracle_trace(void *scene, const float *rays, size_t n, const float *medium_xi, b200pt_hit *hits)
+{
+    return trace_impl(scene, rays, n, medium_xi, hits, 0);
+}
+
+int pt_oracle_trace_shadow(void *scene, const float *rays, size_t n, const float *medium_xi, b200pt_hit *hits)
+{
+    return trace_impl(scene, rays, n, medium_xi, hits, 1);
+}
+
+// emitter flag of every instance (n_inst bytes); returns n_inst
+int pt_oracle_emitters(void *scene, uint8_t *flags)
+{
+    OracleScene *sc = (OracleScene *)scene;
+    for (int i = 0; i < sc->view.n_inst; i++)
+        if (flags)
+            flags[i] = meta_emitter(sc->view.inst[i].meta) ? 1 : 0;
+    return sc->view.n_inst;
 }
 
 // The render loop.  rgb_sums: H x W x 3 float32 sums, row 0 = image bottom (Renderer::framebuffer).

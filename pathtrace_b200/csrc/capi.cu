@@ -125,6 +125,7 @@ void upload_scene(b200pt_scene &sc)
     v.mats = keep(dev_upload(sc.flat.materials));
     v.tex = keep(dev_upload(sc.flat.textures));
     v.lights = keep(dev_upload(sc.flat.lights));
+    v.emitters = keep(dev_upload(sc.packed.emitters));
     v.perlin_ranvec = keep(dev_upload(sc.packed.perlin_ranvec));
     v.perlin_perm = keep(dev_upload(sc.packed.perlin_perm));
 }

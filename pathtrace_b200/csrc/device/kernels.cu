@@ -244,7 +244,8 @@ __global__ void __launch_bounds__(kThreads) k_shade(PtSceneView s, RenderParams 
 #ifndef PT_NEE_MEDIA_MINB
 #define PT_NEE_MEDIA_MINB 3
 #endif
-template <bool COUNT, bool MEDIA>
+// ANY: the scene has at most PT_MAX_DIRECT_EMITTERS emitters -> emitters first, then an any-hit walk (trace_shadow)
+template <bool COUNT, bool MEDIA, bool ANY>
 __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
     TraceCounters tc;
@@ -265,6 +266,8 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
         MediumRng mr;
         mr.xi = -1.f;
         NeeSample ns;
+        bool trace = false;
+        int lit = -1;
         if (e < n) {
             int q, k;
             if (pow2) {
@@ -281,9 +284,14 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
             nee_prepare(s, key, bounce, k, xyz(hp), xyz(hn), __float_as_int(w.w), xyz(w), ns);
             mr = nee_medium_rng(key, bounce, k);
             T.init(xyz(hp), ns.dir, 0.001f, PT_FLT_MAX);
+            trace = !nee_is_void(ns);
+            if (ANY && trace) {
+                trace = T.template emitters_first<COUNT>(s, &tc);
+                lit = T.best_inst;
+            }
         }
-        T.template run_warp<COUNT, MEDIA>(s, slot >= 0, mr, &tc); // all 32 lanes take part in the votes
-        if (slot >= 0) {
+        T.template run_warp<COUNT, MEDIA, ANY>(s, trace, mr, &tc); // all 32 lanes take part in the votes
+        if (trace && (!ANY || T.best_inst == lit)) {
             Hit lrec;
             const bool hit = T.template result<MEDIA>(s, lrec);
             c = nee_finish(s, ns, hit, lrec);
@@ -546,12 +554,23 @@ void launch_shade(const PtSceneView &s, const RenderParams &rp, const Wavefront 
 void launch_nee(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, const LaunchCfg &lc,
                 cudaStream_t st)
 {
-    if (lc.count_work)
-        k_nee<true, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
-    else if (s.n_media > 0)
-        k_nee<false, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
-    else
-        k_nee<false, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+    const bool any = s.n_emitters <= PT_MAX_DIRECT_EMITTERS;
+    if (lc.count_work) {
+        if (any)
+            k_nee<true, true, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+        else
+            k_nee<true, true, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+    } else if (s.n_media > 0) {
+        if (any)
+            k_nee<false, true, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+        else
+            k_nee<false, true, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+    } else {
+        if (any)
+            k_nee<false, false, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+        else
+            k_nee<false, false, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+    }
 }
 
 void launch_accumulate(const RenderParams &rp, const Wavefront &wf, const Film &film, int n_rows, cudaStream_t st)

@@ -324,6 +324,7 @@ struct TraceCounters {
 };
 
 #define PT_STACK_DEPTH 48
+#define PT_MAX_DIRECT_EMITTERS 8 // more emitters than this: shadow rays fall back to the plain closest-hit query
 
 // World::hit (world.h:17-20) as a resumable state machine: init() -> steps until one returns false -> result().
 // A step visits one inner node (node_step) or tests one leaf (leaf_step).  The CPU restatement runs a ray to
@@ -414,12 +415,16 @@ struct Traversal {
     }
 
     // One leaf (cur < 0): the instance ~cur.  Returns false when the traversal is complete.
-    template <bool COUNT, bool MEDIA>
+    // ANY = true is the occlusion phase of a shadow query (see emitters_first): emitters were tested already and the
+    // first accepted hit ends the traversal.
+    template <bool COUNT, bool MEDIA, bool ANY = false>
     PT_HD bool leaf_step(const PtSceneView &s, const MediumRng &mr, TraceCounters *counters)
     {
         const int idx = ~cur;
         InstanceData I;
         load_instance(s.inst, idx, I);
+        if (ANY && meta_emitter(I.meta))
+            return pop();
         PrimHit h;
         if (COUNT)
             counters->prims += 1;
@@ -432,16 +437,44 @@ struct Traversal {
             best_t = h.t;
             best = h;
             best_inst = idx;
+            if (ANY)
+                return false; // occluded: nothing nearer can change the answer
         }
         return pop();
     }
 
+    // Shadow queries (integrator.h:246-252) need only the emission of whatever the ray meets first, and that is zero
+    // unless the first thing is an emitter.  So: the few emitters are intersected directly (closest one wins, same
+    // tie rule), then the BVH is walked for ANY other instance in front of it.  Same answer as the closest-hit
+    // query whenever that answer matters; a ray that meets no emitter is done without touching the BVH.
+    // Returns whether an emitter was hit (best_* hold it).  Requires s.n_emitters <= PT_MAX_DIRECT_EMITTERS.
+    template <bool COUNT> PT_HD bool emitters_first(const PtSceneView &s, TraceCounters *counters)
+    {
+        MediumRng none;
+        none.xi = -1.f;
+        for (int e = 0; e < s.n_emitters; e++) {
+            const int idx = s.emitters[e];
+            InstanceData I;
+            load_instance(s.inst, idx, I);
+            PrimHit h;
+            if (COUNT)
+                counters->prims += 1;
+            if (hit_instance<false>(I, o, d, t_min, best_t, none, h) && (h.t < best_t || idx > best_inst)) {
+                best_t = h.t;
+                best = h;
+                best_inst = idx;
+            }
+        }
+        return best_inst >= 0;
+    }
+
     // one ray run to completion (CPU restatement, and any caller without a warp to vote with)
-    template <bool COUNT, bool MEDIA> PT_HD void run(const PtSceneView &s, const MediumRng &mr, TraceCounters *counters)
+    template <bool COUNT, bool MEDIA, bool ANY = false>
+    PT_HD void run(const PtSceneView &s, const MediumRng &mr, TraceCounters *counters)
     {
         bool more = true;
         while (more)
-            more = cur >= 0 ? node_step<COUNT>(s, counters) : leaf_step<COUNT, MEDIA>(s, mr, counters);
+            more = cur >= 0 ? node_step<COUNT>(s, counters) : leaf_step<COUNT, MEDIA, ANY>(s, mr, counters);
     }
 
 #if defined(__CUDACC__)
@@ -452,9 +485,14 @@ struct Traversal {
     // half of the unfinished lanes in it, and the code of the other kind is not interleaved with it.
     // Must be called by all 32 lanes (`active` = this lane has a ray).  Per ray the sequence of steps is the one
     // run() takes, so the result is identical.
-    template <bool COUNT, bool MEDIA>
+    template <bool COUNT, bool MEDIA, bool ANY = false>
     __device__ __forceinline__ void run_warp(const PtSceneView &s, bool active, const MediumRng &mr, TraceCounters *counters)
     {
+#ifdef PT_LANE_LOOP // A/B: every lane loops on its own
+        if (active)
+            run<COUNT, MEDIA, ANY>(s, mr, counters);
+        return;
+#endif
         while (true) {
             const unsigned m_act = __ballot_sync(0xffffffffu, active);
             if (!m_act)
@@ -465,7 +503,7 @@ struct Traversal {
                     active = node_step<COUNT>(s, counters);
             } else {
                 if (active && cur < 0)
-                    active = leaf_step<COUNT, MEDIA>(s, mr, counters);
+                    active = leaf_step<COUNT, MEDIA, ANY>(s, mr, counters);
             }
         }
     }
@@ -518,6 +556,27 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
     Traversal T;
     T.init(o, d, t_min, t_max);
     T.template run<COUNT, MEDIA>(s, mr, counters);
+    return T.template result<MEDIA>(s, out);
+}
+
+// The shadow query of NEE: true iff the FIRST thing the ray meets is an emitter (out = that hit).  A false return
+// stands for "miss or a non-emitting surface first", which contribute the same nothing.
+template <bool COUNT, bool MEDIA = true>
+PT_HD bool trace_shadow(const PtSceneView &s, V3 o, V3 d, float t_min, float t_max, const MediumRng &mr, Hit &out,
+                        TraceCounters *counters)
+{
+    Traversal T;
+    T.init(o, d, t_min, t_max);
+    if (s.n_emitters > PT_MAX_DIRECT_EMITTERS) {
+        T.template run<COUNT, MEDIA>(s, mr, counters);
+        return T.template result<MEDIA>(s, out);
+    }
+    if (!T.template emitters_first<COUNT>(s, counters))
+        return false;
+    const int32_t lit = T.best_inst;
+    T.template run<COUNT, MEDIA, true>(s, mr, counters);
+    if (T.best_inst != lit)
+        return false;
     return T.template result<MEDIA>(s, out);
 }
 

@@ -23,7 +23,7 @@ struct alignas(16) PtNode {
 };
 
 // meta: bits 0-1 prim kind | 2-3 rect plane | 4 rect flip | 5 medium | 6 bvh-dup | 7 light | 8-15 medium slot |
-//       16-31 material index
+//       16-30 material index | 31 emitter (the material a hit reports is a diffuse_light)
 struct alignas(16) PtInstance {
     float inv[12];
     uint32_t meta;
@@ -42,7 +42,8 @@ PT_HD bool meta_medium(uint32_t m) { return (m >> 5) & 1u; }
 PT_HD bool meta_dup(uint32_t m) { return (m >> 6) & 1u; }
 PT_HD bool meta_light(uint32_t m) { return (m >> 7) & 1u; }
 PT_HD uint32_t meta_medium_slot(uint32_t m) { return (m >> 8) & 0xffu; }
-PT_HD int meta_material(uint32_t m) { return (int)(m >> 16); }
+PT_HD int meta_material(uint32_t m) { return (int)((m >> 16) & 0x7fffu); }
+PT_HD bool meta_emitter(uint32_t m) { return (m >> 31) & 1u; }
 
 struct PtCamera {
     V3 origin, lower_left, horizontal, vertical, u, v;
@@ -56,9 +57,10 @@ struct PtSceneView {
     const b200pt_material *mats;
     const b200pt_texture *tex;
     const int32_t *lights;
+    const int32_t *emitters;    // instances whose hit material emits (shadow rays test these first, pt_intersect.h)
     const float *perlin_ranvec; // 256 x 3
     const int32_t *perlin_perm; // 3 x 256
-    int32_t n_nodes, n_inst, n_lights, background;
+    int32_t n_nodes, n_inst, n_lights, n_emitters, background;
     int32_t n_media; // instances wrapped in a constant_medium; 0 selects the kernels compiled without that branch
     PtCamera cam;
 };

@@ -309,6 +309,13 @@ PT_HD void nee_prepare(const PtSceneView &s, const RngKey &key, int bounce, int 
     out.coef = c;
 }
 
+// a sample whose coefficient is zero or NaN contributes nothing whatever its shadow ray meets (nee_finish turns
+// a NaN product into zero): no ray needs tracing.  The reference's ray counter still counts it (k_tally).
+PT_HD bool nee_is_void(const NeeSample &ns)
+{
+    return is_nan(ns.coef) || (ns.coef.x == 0.f && ns.coef.y == 0.f && ns.coef.z == 0.f);
+}
+
 // lrec: the closest hit of the shadow ray; it starts at the un-offset hit point and t is in units of |dir|
 // (integrator.h:235,246) (sic).  Whatever is hit first contributes its emission -- `true ||` (integrator.h:250) (sic)
 PT_HD V3 nee_finish(const PtSceneView &s, const NeeSample &ns, bool hit, const Hit &lrec)
@@ -339,9 +346,11 @@ PT_HD V3 nee_sample(const PtSceneView &s, const RenderParams &rp, const RngKey &
 {
     NeeSample ns;
     nee_prepare(s, key, bounce, k, p, n, mat_kind, W, ns);
+    if (nee_is_void(ns))
+        return v3(0.f, 0.f, 0.f);
     MediumRng mr = nee_medium_rng(key, bounce, k);
     Hit lrec;
-    bool hit = trace_closest<COUNT, MEDIA>(s, p, ns.dir, 0.001f, PT_FLT_MAX, mr, lrec, counters);
+    bool hit = trace_shadow<COUNT, MEDIA>(s, p, ns.dir, 0.001f, PT_FLT_MAX, mr, lrec, counters);
     return nee_finish(s, ns, hit, lrec);
 }
 

@@ -14,8 +14,8 @@ PackedScene pack_scene(const FlatScene &f)
     const int n = (int)f.instances.size();
     if (n <= 0)
         throw std::runtime_error("scene has no instances");
-    if (f.materials.size() > 65535)
-        throw std::runtime_error("too many materials (16-bit material index)");
+    if (f.materials.size() > 32767)
+        throw std::runtime_error("too many materials (15-bit material index)");
     out.inst.resize(n);
     out.fwd.resize(n);
     std::vector<Aabb> boxes(n);
@@ -42,6 +42,11 @@ PackedScene pack_scene(const FlatScene &f)
         if (src.light_index >= 0)
             meta |= 1u << 7;
         meta |= (uint32_t)src.material << 16;
+        if (src.material >= 0 && src.material < (int)f.materials.size() &&
+            f.materials[src.material].kind == B200PT_MAT_DIFFUSE_LIGHT) {
+            meta |= 1u << 31;
+            out.emitters.push_back(i);
+        }
         dst.meta = meta;
         memcpy(dst.p, src.params, sizeof(dst.p));
         dst.density = src.density;
@@ -67,6 +72,8 @@ pt::PtSceneView PackedScene::host_view(const FlatScene &f) const
     v.mats = f.materials.data();
     v.tex = f.textures.data();
     v.lights = f.lights.data();
+    v.emitters = emitters.data();
+    v.n_emitters = (int)emitters.size();
     v.perlin_ranvec = perlin_ranvec.data();
     v.perlin_perm = perlin_perm.data();
     v.n_nodes = (int)bvh.nodes.size();

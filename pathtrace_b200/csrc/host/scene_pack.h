@@ -14,6 +14,7 @@ struct PackedScene {
     BuiltBvh bvh;
     std::vector<float> perlin_ranvec;  // 768
     std::vector<int32_t> perlin_perm;  // 768
+    std::vector<int32_t> emitters;     // instances whose hit material is a diffuse_light, ascending
     int n_media = 0;
     // a view whose pointers refer to THIS object's host vectors and to `flat`'s material/texture/light arrays
     pt::PtSceneView host_view(const FlatScene &flat) const;

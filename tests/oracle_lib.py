@@ -109,6 +109,8 @@ class PortOracle:
         self.lib.pt_oracle_scene_destroy.argtypes = [C.c_void_p]
         self.lib.pt_oracle_last_error.restype = C.c_char_p
         self.lib.pt_oracle_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+        self.lib.pt_oracle_trace_shadow.argtypes = self.lib.pt_oracle_trace.argtypes
+        self.lib.pt_oracle_emitters.argtypes = [C.c_void_p, C.c_void_p]
         self.lib.pt_oracle_render.argtypes = [C.c_void_p, C.POINTER(_CConfig), C.c_void_p, C.c_void_p, C.c_void_p,
                                               C.POINTER(C.c_int64), C.c_int, C.c_int64, C.c_int64]
         self.h = self.lib.pt_oracle_scene_create(scene_json_text.encode(), w, h)
@@ -133,6 +135,21 @@ class PortOracle:
         self.lib.pt_oracle_trace(self.h, rays.ctypes.data, rays.shape[0], None if xi is None else xi.ctypes.data,
                                  hits.ctypes.data)
         return hits
+
+    def trace_shadow(self, rays, medium_xi=None):
+        """The NEE shadow query (emitters first, then any-hit): a record only when an emitter is met first."""
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+        hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
+        xi = None if medium_xi is None else np.ascontiguousarray(medium_xi, dtype=np.float32)
+        self.lib.pt_oracle_trace_shadow(self.h, rays.ctypes.data, rays.shape[0],
+                                        None if xi is None else xi.ctypes.data, hits.ctypes.data)
+        return hits
+
+    def emitters(self):
+        n = self.lib.pt_oracle_emitters(self.h, None)
+        flags = np.zeros(n, dtype=np.uint8)
+        self.lib.pt_oracle_emitters(self.h, flags.ctypes.data)
+        return flags.astype(bool)
 
     def render(self, cconfig, threads=None, pixel_begin=0, pixel_end=0, stats=True):
         h, w = cconfig.height, cconfig.width

@@ -89,3 +89,32 @@ def test_render_statistics_match_reference(tag):
     ref_rays_per_path = float(g["total_rays"]) / (w * h * n_ref)
     got = out["rays_reference"] / (w * h * n)
     assert abs(got - ref_rays_per_path) < 0.03 * ref_rays_per_path, (got, ref_rays_per_path)
+
+
+@pytest.mark.parametrize("name", SCENE_FILES)
+def test_shadow_query_equals_filtered_closest_hit(name):
+    """NEE's shadow query (emitters first, then an any-hit walk: pt_intersect.h trace_shadow) must report exactly
+    what World::hit reports whenever the first thing met is an emitter, and nothing otherwise -- the only use the
+    reference makes of a shadow hit is its emission (integrator.h:246-252)."""
+    g = np.load(os.path.join(GOLDEN, f"hits_{name}.npz"))
+    oracle = PortOracle.from_file(scene_path(name), W, H)
+    emit = oracle.emitters()
+    assert emit.any()
+    b = _flat(name).bvh_info()["bounds"]
+    extra = raygen.random_rays(b[:3], b[3:], 20000, seed=21)
+    first = oracle.trace(extra, np.full(len(extra), 0.5, np.float32))
+    on_emitters = first["p"][(first["instance"] >= 0) & emit[np.maximum(first["instance"], 0)]]
+    assert len(on_emitters) > 0
+    rays = np.concatenate([g["rays"], extra, raygen.shadow_rays(first, on_emitters, 20000, seed=22)])
+    xi = np.random.default_rng(5).random(len(rays), dtype=np.float32) * 0.98 + 0.01
+    full = oracle.trace(rays, xi)
+    shadow = oracle.trace_shadow(rays, xi)
+    # rays lying IN a rect's plane give t = NaN, which passes rect::hit; the winner then depends on the visiting
+    # order (DESIGN.md, known non-parity).  NEE never traces one: its light pdf is NaN and the sample is dropped.
+    ok = ~(np.isnan(full["t"]) | np.isnan(shadow["t"]))
+    assert ok.mean() > 0.95  # light-to-light shadow rays are in-plane by construction
+    lit = ok & (full["instance"] >= 0) & emit[np.maximum(full["instance"], 0)]
+    assert lit.sum() > 50, "batch does not exercise emitters"
+    assert np.array_equal((shadow["instance"] >= 0)[ok], lit[ok])
+    for f in ("instance", "t", "p", "n"):
+        assert np.array_equal(shadow[f][lit], full[f][lit]), f
