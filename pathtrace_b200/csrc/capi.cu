@@ -126,6 +126,7 @@ void upload_scene(b200pt_scene &sc)
     v.tex = keep(dev_upload(sc.flat.textures));
     v.lights = keep(dev_upload(sc.flat.lights));
     v.emitters = keep(dev_upload(sc.packed.emitters));
+    v.small = keep(dev_upload(sc.packed.small));
     v.perlin_ranvec = keep(dev_upload(sc.packed.perlin_ranvec));
     v.perlin_perm = keep(dev_upload(sc.packed.perlin_perm));
 }

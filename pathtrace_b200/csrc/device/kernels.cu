@@ -25,10 +25,10 @@ __device__ __forceinline__ float4 f4(V3 a, float w) { return make_float4(a.x, a.
 // Block-wide queue reservation: every thread passes a bit mask of the NQ queues it appends to.  Ranks come from
 // warp ballots, warp totals are prefix-summed in shared memory and ONE atomicAdd per (block, queue) reserves the
 // range.  Must be called by all threads of the block.
-template <int NQ>
+template <int NQ, int NW = kWarps>
 __device__ __forceinline__ void block_reserve(unsigned mask, int32_t *const (&counter)[NQ], int (&pos)[NQ])
 {
-    __shared__ int s_cnt[NQ][kWarps];
+    __shared__ int s_cnt[NQ][NW];
     __shared__ int s_base[NQ];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned lt = (1u << lane) - 1u;
@@ -44,7 +44,7 @@ __device__ __forceinline__ void block_reserve(unsigned mask, int32_t *const (&co
     if (threadIdx.x < NQ) {
         int total = 0;
 #pragma unroll
-        for (int w = 0; w < kWarps; w++) {
+        for (int w = 0; w < NW; w++) {
             int c = s_cnt[threadIdx.x][w];
             s_cnt[threadIdx.x][w] = total;
             total += c;
@@ -55,6 +55,17 @@ __device__ __forceinline__ void block_reserve(unsigned mask, int32_t *const (&co
 #pragma unroll
     for (int q = 0; q < NQ; q++)
         pos[q] = s_base[q] + s_cnt[q][warp] + rank[q];
+    __syncthreads();
+}
+
+// the small-scene table -> shared memory (all threads of the block; ends with a barrier)
+__device__ __forceinline__ void stage_small(const PtSceneView &s, PtSmallEntry *dst)
+{
+    const float4 *src = reinterpret_cast<const float4 *>(s.small);
+    float4 *d = reinterpret_cast<float4 *>(dst);
+    const int n4 = s.n_small * (int)(sizeof(PtSmallEntry) / sizeof(float4));
+    for (int i = threadIdx.x; i < n4; i += blockDim.x)
+        d[i] = __ldg(src + i);
     __syncthreads();
 }
 
@@ -121,9 +132,18 @@ __global__ void __launch_bounds__(kThreads) k_raygen(PtSceneView s, RenderParams
     }
 }
 
-template <bool COUNT, bool MEDIA>
-__global__ void __launch_bounds__(kThreads) k_extend(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
+// Small blocks: the queue reservation is a block-wide barrier, and a block waits for its slowest ray -- with 256
+// threads a quarter of all stall samples on the 8192-instance scene were that barrier.
+#ifndef PT_EXT_THREADS
+#define PT_EXT_THREADS 64
+#endif
+constexpr int kExtThreads = PT_EXT_THREADS;
+template <bool COUNT, bool MEDIA, bool SMALL>
+__global__ void __launch_bounds__(kExtThreads) k_extend(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
+    __shared__ PtSmallEntry s_small[SMALL ? PT_SMALL_MAX : 1];
+    if (SMALL)
+        stage_small(s, s_small);
     TraceCounters tc;
     tc.boxes = tc.prims = 0;
     unsigned long long nrays = 0;
@@ -133,7 +153,7 @@ __global__ void __launch_bounds__(kThreads) k_extend(PtSceneView s, RenderParams
     const int32_t *q_in = bounce == 0 ? nullptr : wf.q_ext[bounce & 1];
     int32_t *const kind_counter[SK_COUNT] = {row + CNT_KIND0, row + CNT_KIND0 + 1, row + CNT_KIND0 + 2,
                                              row + CNT_KIND0 + 3, row + CNT_KIND0 + 4};
-    for (int base = blockIdx.x * kThreads; base < n; base += gridDim.x * kThreads) {
+    for (int base = blockIdx.x * kExtThreads; base < n; base += gridDim.x * kExtThreads) {
         const int i = base + threadIdx.x;
         unsigned mask = 0;
         int slot = 0;
@@ -149,7 +169,12 @@ __global__ void __launch_bounds__(kThreads) k_extend(PtSceneView s, RenderParams
             T.init(xyz(ro), xyz(rd), 0.001f, PT_FLT_MAX);
             nrays++;
         }
-        T.template run_warp<COUNT, MEDIA>(s, live, mr, &tc); // all 32 lanes take part in the votes
+        if (SMALL) {
+            if (live)
+                T.template run_small<COUNT, MEDIA>(s_small, s.n_small, mr, &tc);
+        } else {
+            T.template run_warp<COUNT, MEDIA>(s, live, mr, &tc); // all 32 lanes take part in the votes
+        }
         if (live) {
             Hit h;
             int kind = SK_MISS;
@@ -161,7 +186,7 @@ __global__ void __launch_bounds__(kThreads) k_extend(PtSceneView s, RenderParams
             mask = 1u << kind;
         }
         int pos[SK_COUNT];
-        block_reserve<SK_COUNT>(mask, kind_counter, pos);
+        block_reserve<SK_COUNT, kExtThreads / 32>(mask, kind_counter, pos);
         if (mask) {
             int kind = __ffs(mask) - 1;
             wf.q_kind[kind][pos[kind]] = slot;
@@ -245,9 +270,13 @@ __global__ void __launch_bounds__(kThreads) k_shade(PtSceneView s, RenderParams 
 #define PT_NEE_MEDIA_MINB 3
 #endif
 // ANY: the scene has at most PT_MAX_DIRECT_EMITTERS emitters -> emitters first, then an any-hit walk (trace_shadow)
-template <bool COUNT, bool MEDIA, bool ANY>
+template <bool COUNT, bool MEDIA, bool ANY, bool SMALL>
 __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
+    static_assert(ANY || !SMALL, "the small-scene walk is instantiated for the any-hit shadow query only");
+    __shared__ PtSmallEntry s_small[SMALL ? PT_SMALL_MAX : 1];
+    if (SMALL)
+        stage_small(s, s_small);
     TraceCounters tc;
     tc.boxes = tc.prims = 0;
     unsigned long long nrays = 0;
@@ -290,7 +319,14 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
                 lit = T.best_inst;
             }
         }
-        T.template run_warp<COUNT, MEDIA, ANY>(s, trace, mr, &tc); // all 32 lanes take part in the votes
+        // every lane loops on its own here: shadow rays of one vertex sit in adjacent lanes and stay together, the
+        // warp vote of k_extend costs more than it saves (measured on all five scenes)
+        if (trace) {
+            if (SMALL)
+                T.template run_small<COUNT, MEDIA, ANY>(s_small, s.n_small, mr, &tc);
+            else
+                T.template run<COUNT, MEDIA, ANY>(s, mr, &tc);
+        }
         if (trace && (!ANY || T.best_inst == lit)) {
             Hit lrec;
             const bool hit = T.template result<MEDIA>(s, lrec);
@@ -390,11 +426,14 @@ __global__ void k_tally(RenderParams rp, Wavefront wf, int n_rows)
 
 // ---------------------------------------------------------------------------------------------------------------
 
-template <bool COUNT, bool MEDIA>
+template <bool COUNT, bool MEDIA, bool SMALL>
 __global__ void __launch_bounds__(kThreads) k_trace_batch(PtSceneView s, const float *__restrict__ rays, size_t n,
                                                           const float *__restrict__ medium_xi,
                                                           b200pt_hit *__restrict__ hits, unsigned long long *counts)
 {
+    __shared__ PtSmallEntry s_small[SMALL ? PT_SMALL_MAX : 1];
+    if (SMALL)
+        stage_small(s, s_small);
     unsigned long long boxes = 0, prims = 0, nhit = 0;
     for (size_t base = (size_t)blockIdx.x * kThreads; base < n; base += (size_t)gridDim.x * kThreads) {
         const size_t i = base + threadIdx.x;
@@ -415,7 +454,12 @@ __global__ void __launch_bounds__(kThreads) k_trace_batch(PtSceneView s, const f
             mr.xi = medium_xi ? medium_xi[i] : -1.f;
             T.init(v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), b.z, b.w);
         }
-        T.template run_warp<COUNT, MEDIA>(s, live, mr, &tc); // all 32 lanes take part in the votes
+        if (SMALL) {
+            if (live)
+                T.template run_small<COUNT, MEDIA>(s_small, s.n_small, mr, &tc);
+        } else {
+            T.template run_warp<COUNT, MEDIA>(s, live, mr, &tc); // all 32 lanes take part in the votes
+        }
         if (!live)
             continue;
         Hit h;
@@ -537,12 +581,22 @@ void launch_raygen(const PtSceneView &s, const RenderParams &rp, const Wavefront
 void launch_extend(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, const LaunchCfg &lc,
                    cudaStream_t st)
 {
+    const int blocks = lc.blocks * (kThreads / kExtThreads);
+    const bool small = s.n_small > 0;
+#define PT_LAUNCH_EXT(C, M)                                                        \
+    do {                                                                           \
+        if (small)                                                                 \
+            k_extend<C, M, true><<<blocks, kExtThreads, 0, st>>>(s, rp, wf, bounce);  \
+        else                                                                       \
+            k_extend<C, M, false><<<blocks, kExtThreads, 0, st>>>(s, rp, wf, bounce); \
+    } while (0)
     if (lc.count_work)
-        k_extend<true, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+        PT_LAUNCH_EXT(true, true);
     else if (s.n_media > 0)
-        k_extend<false, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+        PT_LAUNCH_EXT(false, true);
     else
-        k_extend<false, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
+        PT_LAUNCH_EXT(false, false);
+#undef PT_LAUNCH_EXT
 }
 
 void launch_shade(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, int kind,
@@ -555,22 +609,23 @@ void launch_nee(const PtSceneView &s, const RenderParams &rp, const Wavefront &w
                 cudaStream_t st)
 {
     const bool any = s.n_emitters <= PT_MAX_DIRECT_EMITTERS;
-    if (lc.count_work) {
-        if (any)
-            k_nee<true, true, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
-        else
-            k_nee<true, true, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
-    } else if (s.n_media > 0) {
-        if (any)
-            k_nee<false, true, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
-        else
-            k_nee<false, true, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
-    } else {
-        if (any)
-            k_nee<false, false, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
-        else
-            k_nee<false, false, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);
-    }
+    const bool small = any && s.n_small > 0;
+#define PT_LAUNCH_NEE(C, M)                                                            \
+    do {                                                                               \
+        if (small)                                                                     \
+            k_nee<C, M, true, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);   \
+        else if (any)                                                                  \
+            k_nee<C, M, true, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);  \
+        else                                                                           \
+            k_nee<C, M, false, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce); \
+    } while (0)
+    if (lc.count_work)
+        PT_LAUNCH_NEE(true, true);
+    else if (s.n_media > 0)
+        PT_LAUNCH_NEE(false, true);
+    else
+        PT_LAUNCH_NEE(false, false);
+#undef PT_LAUNCH_NEE
 }
 
 void launch_accumulate(const RenderParams &rp, const Wavefront &wf, const Film &film, int n_rows, cudaStream_t st)
@@ -587,12 +642,21 @@ void launch_trace_batch(const PtSceneView &s, const float *rays, size_t n, const
         return;
     size_t want = (n + kThreads - 1) / kThreads;
     int blocks = (int)(want < (size_t)(148 * 16) ? want : (size_t)(148 * 16));
+    const bool small = s.n_small > 0;
+#define PT_LAUNCH_TB(C, M, cnt)                                                                      \
+    do {                                                                                             \
+        if (small)                                                                                   \
+            k_trace_batch<C, M, true><<<blocks, kThreads, 0, st>>>(s, rays, n, medium_xi, hits, cnt);  \
+        else                                                                                         \
+            k_trace_batch<C, M, false><<<blocks, kThreads, 0, st>>>(s, rays, n, medium_xi, hits, cnt); \
+    } while (0)
     if (counts)
-        k_trace_batch<true, true><<<blocks, kThreads, 0, st>>>(s, rays, n, medium_xi, hits, counts);
+        PT_LAUNCH_TB(true, true, counts);
     else if (s.n_media > 0)
-        k_trace_batch<false, true><<<blocks, kThreads, 0, st>>>(s, rays, n, medium_xi, hits, nullptr);
+        PT_LAUNCH_TB(false, true, nullptr);
     else
-        k_trace_batch<false, false><<<blocks, kThreads, 0, st>>>(s, rays, n, medium_xi, hits, nullptr);
+        PT_LAUNCH_TB(false, false, nullptr);
+#undef PT_LAUNCH_TB
 }
 
 void launch_luminance(const float4 *accum, int npix, float inv_n, float *max_total, cudaStream_t st)

@@ -468,6 +468,62 @@ struct Traversal {
         return best_inst >= 0;
     }
 
+    // Small scenes: no tree.  All instances in index order; a rect (most of a Cornell box) is tested directly --
+    // its t needs one row of the transform, the rest is computed only when t is in range -- anything else behind
+    // the slab test of its leaf box, exactly the test the tree would have made.  The closest hit is the same:
+    // every primitive test depends on (ray, t_min, best_t) only and ties go to the higher index either way.
+    // On the GPU the 32 lanes walk the table together (tab in shared memory): no stack, no divergence between
+    // primitive kinds.
+    template <bool COUNT, bool MEDIA, bool ANY = false>
+    PT_HD void run_small(const PtSmallEntry *tab, int n, const MediumRng &mr, TraceCounters *counters)
+    {
+        for (int idx = 0; idx < n; idx++) {
+            const PtSmallEntry &E = tab[idx];
+            const uint32_t meta = E.inst.meta;
+            if (ANY && meta_emitter(meta))
+                continue;
+            PrimHit h;
+            bool ok;
+            if (meta_kind(meta) == B200PT_PRIM_RECT && !(MEDIA && meta_medium(meta))) {
+                if (COUNT)
+                    counters->prims += 1;
+                // shuffle() puts the plane's axis in .y: XY -> local z, YZ -> local x, XZ -> local y
+                const int plane = meta_plane(meta);
+                const float *row = E.inst.inv + (plane == B200PT_PLANE_XY ? 8 : (plane == B200PT_PLANE_YZ ? 0 : 4));
+                const float oy = row[0] * o.x + row[1] * o.y + row[2] * o.z + row[3]; // xform_point, that row
+                const float dy = row[0] * d.x + row[1] * d.y + row[2] * d.z;          // xform_vector, that row
+                const float t = (E.inst.p[4] - oy) / dy;
+                if (t < t_min || t > best_t) // rect::hit's own range test (a NaN t passes)
+                    continue;
+                ok = hit_rect(plane, meta_flip(meta), E.inst.p[0], E.inst.p[1], E.inst.p[2], E.inst.p[3], E.inst.p[4],
+                              xform_point(E.inst.inv, o), xform_vector(E.inst.inv, d), t_min, best_t, h);
+            } else {
+                float entry;
+                if (COUNT)
+                    counters->boxes += 1;
+                if (!hit_aabb(E.lo, E.hi, o, inv_d, t_min, cull_limit(best_t), entry))
+                    continue;
+                if (COUNT)
+                    counters->prims += 1;
+                InstanceData I;
+                for (int k = 0; k < 12; k++)
+                    I.inv[k] = E.inst.inv[k];
+                I.meta = meta;
+                for (int k = 0; k < 6; k++)
+                    I.p[k] = E.inst.p[k];
+                I.density = E.inst.density;
+                ok = hit_instance<MEDIA>(I, o, d, t_min, best_t, mr, h);
+            }
+            if (ok && (h.t < best_t || idx > best_inst)) {
+                best_t = h.t;
+                best = h;
+                best_inst = idx;
+                if (ANY)
+                    return;
+            }
+        }
+    }
+
     // one ray run to completion (CPU restatement, and any caller without a warp to vote with)
     template <bool COUNT, bool MEDIA, bool ANY = false>
     PT_HD void run(const PtSceneView &s, const MediumRng &mr, TraceCounters *counters)
@@ -555,7 +611,10 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
 {
     Traversal T;
     T.init(o, d, t_min, t_max);
-    T.template run<COUNT, MEDIA>(s, mr, counters);
+    if (s.n_small > 0)
+        T.template run_small<COUNT, MEDIA>(s.small, s.n_small, mr, counters);
+    else
+        T.template run<COUNT, MEDIA>(s, mr, counters);
     return T.template result<MEDIA>(s, out);
 }
 
@@ -574,7 +633,10 @@ PT_HD bool trace_shadow(const PtSceneView &s, V3 o, V3 d, float t_min, float t_m
     if (!T.template emitters_first<COUNT>(s, counters))
         return false;
     const int32_t lit = T.best_inst;
-    T.template run<COUNT, MEDIA, true>(s, mr, counters);
+    if (s.n_small > 0)
+        T.template run_small<COUNT, MEDIA, true>(s.small, s.n_small, mr, counters);
+    else
+        T.template run<COUNT, MEDIA, true>(s, mr, counters);
     if (T.best_inst != lit)
         return false;
     return T.template result<MEDIA>(s, out);

@@ -1,6 +1,8 @@
 #include "scene_pack.h"
 
+#include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <stdexcept>
 #include <string>
 
@@ -54,6 +56,22 @@ PackedScene pack_scene(const FlatScene &f)
     }
     out.n_media = media;
     out.bvh = build_bvh(boxes);
+    // B200PT_SMALL_MAX (tests, A/B): 0 forces the BVH path on small scenes too
+    int small_max = PT_SMALL_MAX;
+    if (const char *e = std::getenv("B200PT_SMALL_MAX"))
+        small_max = std::min(PT_SMALL_MAX, std::max(0, atoi(e)));
+    if (n <= small_max) {
+        out.small.resize(n);
+        for (int i = 0; i < n; i++) {
+            pt::PtSmallEntry &e = out.small[i];
+            for (int k = 0; k < 3; k++) {
+                e.lo[k] = boxes[i].lo[k];
+                e.hi[k] = boxes[i].hi[k];
+            }
+            e.pad0 = e.pad1 = 0.f;
+            e.inst = out.inst[i];
+        }
+    }
     out.perlin_ranvec = f.perlin_ranvec;
     out.perlin_perm = f.perlin_perm;
     if (out.perlin_ranvec.size() != 768)
@@ -73,6 +91,8 @@ pt::PtSceneView PackedScene::host_view(const FlatScene &f) const
     v.tex = f.textures.data();
     v.lights = f.lights.data();
     v.emitters = emitters.data();
+    v.small = small.data();
+    v.n_small = (int)small.size();
     v.n_emitters = (int)emitters.size();
     v.perlin_ranvec = perlin_ranvec.data();
     v.perlin_perm = perlin_perm.data();

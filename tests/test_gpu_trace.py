@@ -161,3 +161,34 @@ def test_empty_and_errors():
     with pytest.raises(pt.B200ptError) as e:
         host_only.trace_batch(np.zeros((4, 8), dtype=np.float32))
     assert e.value.code == 3  # B200PT_ERR_NO_DEVICE: no CPU fallback
+
+
+@pytest.mark.parametrize("name", [n for n in SCENE_FILES if n != "book2_final"])
+def test_small_scene_walk_equals_tree_walk(name, monkeypatch):
+    """Scenes of <= PT_SMALL_MAX instances are traced without the tree (pt_intersect.h run_small).  With
+    B200PT_SMALL_MAX=0 the same scene goes through the BVH kernels: records must be equal bit for bit, and a small
+    render must give the same film (the shadow query differs too: any-hit over the table vs over the tree)."""
+    import pathtrace_b200 as pt
+    small = _scene(name)
+    monkeypatch.setenv("B200PT_SMALL_MAX", "0")
+    tree = _scene(name)
+    monkeypatch.delenv("B200PT_SMALL_MAX")
+    flat = small.describe()
+    cam_rays, rnd = _batches(small, flat)
+    sec = raygen.secondary_rays(small.trace_batch(cam_rays), 20000, seed=3)
+    rays = np.concatenate([cam_rays, rnd, sec])
+    xi = np.random.Generator(np.random.PCG64(5)).random(len(rays), dtype=np.float32) * 0.999 + 0.0005
+    a, b = small.trace_batch(rays, xi), tree.trace_batch(rays, xi)
+    ok = ~(np.isnan(a["t"]) | np.isnan(b["t"]))  # rays IN a rect's plane: order-dependent winner (DESIGN.md)
+    assert ok.mean() > 0.999
+    for f in ("instance", "t", "p", "n", "u", "v"):
+        assert np.array_equal(a[f][ok], b[f][ok]), f
+    cfgd = pt.default_config_dict(width=W, height=H, samples=8, scene=scene_path(name))
+    films = []
+    for sc in (small, tree):
+        r = pt.renderer_from_config(sc, pt.Config.from_json(cfgd)).start_render()
+        rep = r.finalize()
+        films.append((r.framebuffer.copy(), rep["rays_extension"], rep["rays_shadow"]))
+        r.close()
+    assert films[0][1:] == films[1][1:]
+    np.testing.assert_allclose(films[0][0], films[1][0], rtol=0, atol=1e-4 * max(1.0, float(np.abs(films[1][0]).max())))
