@@ -153,6 +153,8 @@ void pt_oracle_scene_destroy(void *scene) { delete (OracleScene *)scene; }
 static int trace_impl(void *scene, const float *rays, size_t n, const float *medium_xi, b200pt_hit *hits, int shadow)
 {
     OracleScene *sc = (OracleScene *)scene;
+    PtSceneView view = sc->view;
+    view.emit_needs_p = 1; // report p of shadow hits too (renders skip it when every emitter has a constant texture)
     for (size_t i = 0; i < n; i++) {
         const float *q = rays + i * 8;
         MediumRng mr;
@@ -162,8 +164,8 @@ static int trace_impl(void *scene, const float *rays, size_t n, const float *med
         mr.stage = stage_word(0, RNG_BATCH_MEDIUM, 0);
         mr.xi = medium_xi ? medium_xi[i] : -1.f;
         Hit h;
-        bool ok = shadow ? trace_shadow<false>(sc->view, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7], mr, h, nullptr)
-                         : trace_closest<false>(sc->view, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7], mr, h, nullptr);
+        bool ok = shadow ? trace_shadow<false>(view, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7], mr, h, nullptr)
+                         : trace_closest<false>(view, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7], mr, h, nullptr);
         b200pt_hit &o = hits[i];
         memset(&o, 0, sizeof(o));
         o.instance = -1;

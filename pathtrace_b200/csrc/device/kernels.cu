@@ -58,16 +58,30 @@ __device__ __forceinline__ void block_reserve(unsigned mask, int32_t *const (&co
     __syncthreads();
 }
 
-// the small-scene table -> shared memory (all threads of the block; ends with a barrier)
-__device__ __forceinline__ void stage_small(const PtSceneView &s, PtSmallEntry *dst)
-{
-    const float4 *src = reinterpret_cast<const float4 *>(s.small);
-    float4 *d = reinterpret_cast<float4 *>(dst);
-    const int n4 = s.n_small * (int)(sizeof(PtSmallEntry) / sizeof(float4));
-    for (int i = threadIdx.x; i < n4; i += blockDim.x)
-        d[i] = __ldg(src + i);
-    __syncthreads();
-}
+// A small scene in shared memory: stage() copies boxes, instances and forward transforms and points the view at
+// the copies, so that nothing on the path of a ray reads the scene from global memory (materials aside).
+struct SmallScene {
+    PtBox box[PT_SMALL_MAX];
+    PtInstance inst[PT_SMALL_MAX];
+    PtFwd fwd[PT_SMALL_MAX];
+
+    __device__ __forceinline__ void stage(PtSceneView &s) // all threads of the block; ends with a barrier
+    {
+        const int n = s.n_small;
+        copy16(box, s.small, n * (int)(sizeof(PtBox) / 16));
+        copy16(inst, s.inst, n * (int)(sizeof(PtInstance) / 16));
+        copy16(fwd, s.fwd, n * (int)(sizeof(PtFwd) / 16));
+        __syncthreads();
+        s.small = box;
+        s.inst = inst;
+        s.fwd = fwd;
+    }
+    static __device__ __forceinline__ void copy16(void *dst, const void *src, int n16)
+    {
+        for (int i = threadIdx.x; i < n16; i += blockDim.x)
+            reinterpret_cast<float4 *>(dst)[i] = __ldg(reinterpret_cast<const float4 *>(src) + i);
+    }
+};
 
 // work counters of one thread -> global totals (profile == 2 only)
 __device__ __forceinline__ void flush_counts(const TraceCounters &tc, unsigned long long rays, unsigned long long *dst)
@@ -141,9 +155,9 @@ constexpr int kExtThreads = PT_EXT_THREADS;
 template <bool COUNT, bool MEDIA, bool SMALL>
 __global__ void __launch_bounds__(kExtThreads) k_extend(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
-    __shared__ PtSmallEntry s_small[SMALL ? PT_SMALL_MAX : 1];
+    __shared__ SmallScene s_small; // dropped by the compiler when SMALL is false
     if (SMALL)
-        stage_small(s, s_small);
+        s_small.stage(s);
     TraceCounters tc;
     tc.boxes = tc.prims = 0;
     unsigned long long nrays = 0;
@@ -171,7 +185,7 @@ __global__ void __launch_bounds__(kExtThreads) k_extend(PtSceneView s, RenderPar
         }
         if (SMALL) {
             if (live)
-                T.template run_small<COUNT, MEDIA>(s_small, s.n_small, mr, &tc);
+                T.template run_small<COUNT, MEDIA>(s.small, s.inst, s.n_small, mr, &tc);
         } else {
             T.template run_warp<COUNT, MEDIA>(s, live, mr, &tc); // all 32 lanes take part in the votes
         }
@@ -274,9 +288,9 @@ template <bool COUNT, bool MEDIA, bool ANY, bool SMALL>
 __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
     static_assert(ANY || !SMALL, "the small-scene walk is instantiated for the any-hit shadow query only");
-    __shared__ PtSmallEntry s_small[SMALL ? PT_SMALL_MAX : 1];
+    __shared__ SmallScene s_small; // dropped by the compiler when SMALL is false
     if (SMALL)
-        stage_small(s, s_small);
+        s_small.stage(s);
     TraceCounters tc;
     tc.boxes = tc.prims = 0;
     unsigned long long nrays = 0;
@@ -315,7 +329,7 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
             T.init(xyz(hp), ns.dir, 0.001f, PT_FLT_MAX);
             trace = !nee_is_void(ns);
             if (ANY && trace) {
-                trace = T.template emitters_first<COUNT>(s, &tc);
+                trace = T.template emitters_first<COUNT>(s, &tc, ns.known_inst, &ns.known);
                 lit = T.best_inst;
             }
         }
@@ -323,26 +337,38 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
         // warp vote of k_extend costs more than it saves (measured on all five scenes)
         if (trace) {
             if (SMALL)
-                T.template run_small<COUNT, MEDIA, ANY>(s_small, s.n_small, mr, &tc);
+                T.template run_small<COUNT, MEDIA, ANY>(s.small, s.inst, s.n_small, mr, &tc);
             else
                 T.template run<COUNT, MEDIA, ANY>(s, mr, &tc);
         }
         if (trace && (!ANY || T.best_inst == lit)) {
             Hit lrec;
-            const bool hit = T.template result<MEDIA>(s, lrec);
+            const bool hit = T.template result<MEDIA>(s, lrec, !ANY || s.emit_needs_p != 0);
             c = nee_finish(s, ns, hit, lrec);
         }
         if (pow2) {
-            // lanes [g*L, (g+1)*L) hold one vertex (kThreads and 32 are multiples of L)
-            for (int off = 1; off < L; off <<= 1) {
-                c.x += __shfl_xor_sync(0xffffffffu, c.x, off);
-                c.y += __shfl_xor_sync(0xffffffffu, c.y, off);
-                c.z += __shfl_xor_sync(0xffffffffu, c.z, off);
+            // lanes [g*L, (g+1)*L) hold one vertex (kThreads and 32 are multiples of L): fixed-order butterfly over
+            // the group.  Five unconditional stages (the stages >= L are discarded) keep the shuffles out of
+            // divergent control flow.
+            __syncwarp();
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const float x = __shfl_xor_sync(0xffffffffu, c.x, off);
+                const float y = __shfl_xor_sync(0xffffffffu, c.y, off);
+                const float z = __shfl_xor_sync(0xffffffffu, c.z, off);
+                if (off < L) {
+                    c.x += x;
+                    c.y += y;
+                    c.z += z;
+                }
             }
             if (slot >= 0 && (threadIdx.x & (L - 1)) == 0 && (c.x != 0.f || c.y != 0.f || c.z != 0.f)) {
-                float4 acc = wf.sum[slot];
-                wf.sum[slot] =
-                    make_float4(acc.x + c.x / inv_L_div, acc.y + c.y / inv_L_div, acc.z + c.z / inv_L_div, 0.f);
+                // one lane per vertex and kernel touches sum[slot]: a reduction without a return value is as
+                // deterministic as load-add-store and does not wait for the load
+                float *dst = reinterpret_cast<float *>(wf.sum + slot);
+                atomicAdd(dst + 0, c.x / inv_L_div);
+                atomicAdd(dst + 1, c.y / inv_L_div);
+                atomicAdd(dst + 2, c.z / inv_L_div);
             }
         } else if (slot >= 0) {
             float *dst = reinterpret_cast<float *>(wf.sum + slot);
@@ -431,9 +457,9 @@ __global__ void __launch_bounds__(kThreads) k_trace_batch(PtSceneView s, const f
                                                           const float *__restrict__ medium_xi,
                                                           b200pt_hit *__restrict__ hits, unsigned long long *counts)
 {
-    __shared__ PtSmallEntry s_small[SMALL ? PT_SMALL_MAX : 1];
+    __shared__ SmallScene s_small; // dropped by the compiler when SMALL is false
     if (SMALL)
-        stage_small(s, s_small);
+        s_small.stage(s);
     unsigned long long boxes = 0, prims = 0, nhit = 0;
     for (size_t base = (size_t)blockIdx.x * kThreads; base < n; base += (size_t)gridDim.x * kThreads) {
         const size_t i = base + threadIdx.x;
@@ -456,7 +482,7 @@ __global__ void __launch_bounds__(kThreads) k_trace_batch(PtSceneView s, const f
         }
         if (SMALL) {
             if (live)
-                T.template run_small<COUNT, MEDIA>(s_small, s.n_small, mr, &tc);
+                T.template run_small<COUNT, MEDIA>(s.small, s.inst, s.n_small, mr, &tc);
         } else {
             T.template run_warp<COUNT, MEDIA>(s, live, mr, &tc); // all 32 lanes take part in the votes
         }

@@ -262,7 +262,8 @@ PT_HD void load_instance(const PtInstance *table, int idx, InstanceData &I)
 {
 #if defined(__CUDA_ARCH__)
     const float4 *q = reinterpret_cast<const float4 *>(table + idx);
-    float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3), e = __ldg(q + 4);
+    // plain loads: `table` is in global memory, or in shared memory for small scenes (kernels.cu SmallScene)
+    float4 a = q[0], b = q[1], c = q[2], d = q[3], e = q[4];
     I.inv[0] = a.x, I.inv[1] = a.y, I.inv[2] = a.z, I.inv[3] = a.w;
     I.inv[4] = b.x, I.inv[5] = b.y, I.inv[6] = b.z, I.inv[7] = b.w;
     I.inv[8] = c.x, I.inv[9] = c.y, I.inv[10] = c.z, I.inv[11] = c.w;
@@ -448,12 +449,24 @@ struct Traversal {
     // tie rule), then the BVH is walked for ANY other instance in front of it.  Same answer as the closest-hit
     // query whenever that answer matters; a ray that meets no emitter is done without touching the BVH.
     // Returns whether an emitter was hit (best_* hold it).  Requires s.n_emitters <= PT_MAX_DIRECT_EMITTERS.
-    template <bool COUNT> PT_HD bool emitters_first(const PtSceneView &s, TraceCounters *counters)
+    // known_inst >= 0: that emitter's hit over (t_min, FLT_MAX) is already known (NEE has just intersected the light
+    // it sampled to get its pdf, pt_shade.h light_pdf_value): `known` is taken as is and the instance is not
+    // intersected again.
+    template <bool COUNT>
+    PT_HD bool emitters_first(const PtSceneView &s, TraceCounters *counters, int known_inst = -1,
+                              const PrimHit *known = nullptr)
     {
         MediumRng none;
         none.xi = -1.f;
+        if (known_inst >= 0) {
+            best_t = known->t;
+            best = *known;
+            best_inst = known_inst;
+        }
         for (int e = 0; e < s.n_emitters; e++) {
             const int idx = s.emitters[e];
+            if (idx == known_inst)
+                continue;
             InstanceData I;
             load_instance(s.inst, idx, I);
             PrimHit h;
@@ -475,11 +488,12 @@ struct Traversal {
     // On the GPU the 32 lanes walk the table together (tab in shared memory): no stack, no divergence between
     // primitive kinds.
     template <bool COUNT, bool MEDIA, bool ANY = false>
-    PT_HD void run_small(const PtSmallEntry *tab, int n, const MediumRng &mr, TraceCounters *counters)
+    PT_HD void run_small(const PtBox *boxes, const PtInstance *table, int n, const MediumRng &mr,
+                         TraceCounters *counters)
     {
         for (int idx = 0; idx < n; idx++) {
-            const PtSmallEntry &E = tab[idx];
-            const uint32_t meta = E.inst.meta;
+            const PtInstance &E = table[idx];
+            const uint32_t meta = E.meta;
             if (ANY && meta_emitter(meta))
                 continue;
             PrimHit h;
@@ -489,29 +503,24 @@ struct Traversal {
                     counters->prims += 1;
                 // shuffle() puts the plane's axis in .y: XY -> local z, YZ -> local x, XZ -> local y
                 const int plane = meta_plane(meta);
-                const float *row = E.inst.inv + (plane == B200PT_PLANE_XY ? 8 : (plane == B200PT_PLANE_YZ ? 0 : 4));
+                const float *row = E.inv + (plane == B200PT_PLANE_XY ? 8 : (plane == B200PT_PLANE_YZ ? 0 : 4));
                 const float oy = row[0] * o.x + row[1] * o.y + row[2] * o.z + row[3]; // xform_point, that row
                 const float dy = row[0] * d.x + row[1] * d.y + row[2] * d.z;          // xform_vector, that row
-                const float t = (E.inst.p[4] - oy) / dy;
+                const float t = (E.p[4] - oy) / dy;
                 if (t < t_min || t > best_t) // rect::hit's own range test (a NaN t passes)
                     continue;
-                ok = hit_rect(plane, meta_flip(meta), E.inst.p[0], E.inst.p[1], E.inst.p[2], E.inst.p[3], E.inst.p[4],
-                              xform_point(E.inst.inv, o), xform_vector(E.inst.inv, d), t_min, best_t, h);
+                ok = hit_rect(plane, meta_flip(meta), E.p[0], E.p[1], E.p[2], E.p[3], E.p[4],
+                              xform_point(E.inv, o), xform_vector(E.inv, d), t_min, best_t, h);
             } else {
                 float entry;
                 if (COUNT)
                     counters->boxes += 1;
-                if (!hit_aabb(E.lo, E.hi, o, inv_d, t_min, cull_limit(best_t), entry))
+                if (!hit_aabb(boxes[idx].lo, boxes[idx].hi, o, inv_d, t_min, cull_limit(best_t), entry))
                     continue;
                 if (COUNT)
                     counters->prims += 1;
                 InstanceData I;
-                for (int k = 0; k < 12; k++)
-                    I.inv[k] = E.inst.inv[k];
-                I.meta = meta;
-                for (int k = 0; k < 6; k++)
-                    I.p[k] = E.inst.p[k];
-                I.density = E.inst.density;
+                load_instance(table, idx, I);
                 ok = hit_instance<MEDIA>(I, o, d, t_min, best_t, mr, h);
             }
             if (ok && (h.t < best_t || idx > best_inst)) {
@@ -566,7 +575,8 @@ struct Traversal {
 #endif
 
     // instance::hit epilogue (primitive.h:302-305): p and normal back to world space, rec.u / rec.v
-    template <bool MEDIA> PT_HD bool result(const PtSceneView &s, Hit &out) const
+    // want_p = false (shadow hits on emitters with constant textures): only instance, t and normal are filled in
+    template <bool MEDIA> PT_HD bool result(const PtSceneView &s, Hit &out, bool want_p = true) const
     {
         if (best_inst < 0) {
             out.inst = -1;
@@ -574,6 +584,14 @@ struct Traversal {
         }
         InstanceData I;
         load_instance(s.inst, best_inst, I);
+        if (!want_p) {
+            out.inst = best_inst;
+            out.t = best.t;
+            out.p = v3(0.f, 0.f, 0.f);
+            out.n = eigen_normalized(xform_vector_transposed(I.inv, best.n));
+            out.u = out.v = 0.f;
+            return true;
+        }
         V3 lo = xform_point(I.inv, o);
         V3 ld = xform_vector(I.inv, d);
         V3 pl = lo + best.t * ld;
@@ -612,7 +630,7 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
     Traversal T;
     T.init(o, d, t_min, t_max);
     if (s.n_small > 0)
-        T.template run_small<COUNT, MEDIA>(s.small, s.n_small, mr, counters);
+        T.template run_small<COUNT, MEDIA>(s.small, s.inst, s.n_small, mr, counters);
     else
         T.template run<COUNT, MEDIA>(s, mr, counters);
     return T.template result<MEDIA>(s, out);
@@ -622,7 +640,7 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
 // stands for "miss or a non-emitting surface first", which contribute the same nothing.
 template <bool COUNT, bool MEDIA = true>
 PT_HD bool trace_shadow(const PtSceneView &s, V3 o, V3 d, float t_min, float t_max, const MediumRng &mr, Hit &out,
-                        TraceCounters *counters)
+                        TraceCounters *counters, int known_inst = -1, const PrimHit *known = nullptr)
 {
     Traversal T;
     T.init(o, d, t_min, t_max);
@@ -630,16 +648,16 @@ PT_HD bool trace_shadow(const PtSceneView &s, V3 o, V3 d, float t_min, float t_m
         T.template run<COUNT, MEDIA>(s, mr, counters);
         return T.template result<MEDIA>(s, out);
     }
-    if (!T.template emitters_first<COUNT>(s, counters))
+    if (!T.template emitters_first<COUNT>(s, counters, known_inst, known))
         return false;
     const int32_t lit = T.best_inst;
     if (s.n_small > 0)
-        T.template run_small<COUNT, MEDIA, true>(s.small, s.n_small, mr, counters);
+        T.template run_small<COUNT, MEDIA, true>(s.small, s.inst, s.n_small, mr, counters);
     else
         T.template run<COUNT, MEDIA, true>(s, mr, counters);
     if (T.best_inst != lit)
         return false;
-    return T.template result<MEDIA>(s, out);
+    return T.template result<MEDIA>(s, out, s.emit_needs_p != 0);
 }
 
 } // namespace pt

@@ -3,7 +3,7 @@
 //   PtNode      64 B  one BVH2 node = two 32-byte child halves {lo.xyz, ref | hi.xyz, pad}; a half is what a ray
 //                     tests (slab test) before descending, fetched as 2 x 128-bit loads.
 //   PtInstance  80 B  world->local 3x4 (48 B) + tagged-union primitive (32 B): meta word, 6 params, density.
-//   PtSmallEntry 112 B small scenes only: leaf box + PtInstance, walked linearly instead of the tree.
+//   PtBox       32 B  small scenes only: the leaf box of every instance, walked linearly instead of the tree.
 //   PtFwd       48 B  local->world 3x4, fetched only for the closest hit and for light sampling.
 //   b200pt_material / b200pt_texture (32 B each) are used as they come from the C ABI.
 #pragma once
@@ -32,16 +32,15 @@ struct alignas(16) PtInstance {
     float density;
 };
 
-// Small scenes (<= PT_SMALL_MAX instances; every Cornell-box config) skip the tree: the table below is walked front
-// to back by all 32 lanes together (pt_intersect.h run_small), staged in shared memory by the kernels.
-// 112 B = world-space box of the instance (the BVH leaf box) + its PtInstance.
+// Small scenes (<= PT_SMALL_MAX instances; every Cornell-box config) skip the tree: all instances are walked in
+// index order by the 32 lanes together (pt_intersect.h run_small), each behind the slab test of its leaf box
+// (PtBox, 32 B).  The kernels keep boxes, instances and forward transforms of such a scene in shared memory.
 #define PT_SMALL_MAX 16
-struct alignas(16) PtSmallEntry {
+struct alignas(16) PtBox {
     float lo[3];
     float pad0;
     float hi[3];
     float pad1;
-    PtInstance inst;
 };
 
 struct alignas(16) PtFwd {
@@ -70,11 +69,12 @@ struct PtSceneView {
     const b200pt_material *mats;
     const b200pt_texture *tex;
     const int32_t *lights;
-    const PtSmallEntry *small;  // n_small entries, index = instance index; n_small == 0: use the BVH
+    const PtBox *small;         // n_small leaf boxes, index = instance index; n_small == 0: use the BVH
     const int32_t *emitters;    // instances whose hit material emits (shadow rays test these first, pt_intersect.h)
     const float *perlin_ranvec; // 256 x 3
     const int32_t *perlin_perm; // 3 x 256
     int32_t n_nodes, n_inst, n_lights, n_emitters, n_small, background;
+    int32_t emit_needs_p; // some emitter has a non-constant texture: shadow hits must report p (else only the normal)
     int32_t n_media; // instances wrapped in a constant_medium; 0 selects the kernels compiled without that branch
     PtCamera cam;
 };

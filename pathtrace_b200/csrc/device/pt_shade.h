@@ -235,14 +235,15 @@ PT_HD V3 light_random(const InstanceData &I, const float *fwd, V3 o, float r1, f
     return xform_vector(fwd, dl);
 }
 
-PT_HD float light_pdf_value(const InstanceData &I, V3 o, V3 v)
+// rec: the light's own hit record for the ray (o, v) over (0.001, FLT_MAX), valid when the pdf is > 0 -- the same
+// record instance::hit would produce, so a shadow query along (o, v) need not intersect this light again.
+PT_HD float light_pdf_value(const InstanceData &I, V3 o, V3 v, PrimHit &rec)
 {
     int kind = meta_kind(I.meta);
     if (meta_medium(I.meta) || kind == B200PT_PRIM_BOX)
         return 0.f; // hittable::pdf_value default (hittable.h:27)
     V3 lo = xform_point(I.inv, o);
     V3 lv = xform_vector(I.inv, v);
-    PrimHit rec;
     if (kind == B200PT_PRIM_RECT) {
         // rect::pdf_value (primitive.h:156-171): all lengths are LOCAL-space lengths (sic)
         if (hit_rect(meta_plane(I.meta), meta_flip(I.meta), I.p[0], I.p[1], I.p[2], I.p[3], I.p[4], lo, lv, 0.001f,
@@ -267,6 +268,12 @@ PT_HD float light_pdf_value(const InstanceData &I, V3 o, V3 v)
     return 0.f;
 }
 
+PT_HD float light_pdf_value(const InstanceData &I, V3 o, V3 v)
+{
+    PrimHit rec;
+    return light_pdf_value(I, o, v, rec);
+}
+
 PT_HD float power_heuristic(float f, float g)
 {
     // helpers.h:138-144 with nf = ng = 1, pow = 2
@@ -283,6 +290,8 @@ struct NeeSample {
     V3 dir;  // shadow ray direction, un-normalised: the light point minus p (integrator.h:235)
     V3 coef; // attenuation * beta * weight_l / light_pdf_l * max(cos_l, 0)
     float pick_pdf;
+    int known_inst; // >= 0: the sampled light is an emitter and `known` is its hit record along dir (light_pdf_value)
+    PrimHit known;
 };
 
 PT_HD void nee_prepare(const PtSceneView &s, const RngKey &key, int bounce, int k, V3 p, V3 n, int mat_kind, V3 W,
@@ -298,7 +307,8 @@ PT_HD void nee_prepare(const PtSceneView &s, const RngKey &key, int bounce, int 
     load_instance(s.inst, light_inst, L);
     V3 dir = light_random(L, s.fwd[light_inst].m, p, r.y, r.z);
     float cos_l = dot(unit_vector(dir), unit_vector(n));
-    float light_pdf_l = light_pdf_value(L, p, dir);
+    float light_pdf_l = light_pdf_value(L, p, dir, out.known);
+    out.known_inst = light_pdf_l > 0.f && meta_emitter(L.meta) ? light_inst : -1;
     float scatter_pdf_l = mat_value(mat_kind, n, dir);
     float weight_l = power_heuristic(light_pdf_l, scatter_pdf_l);
     float dropoff = fmaxf(cos_l, 0.0f);
@@ -350,7 +360,7 @@ PT_HD V3 nee_sample(const PtSceneView &s, const RenderParams &rp, const RngKey &
         return v3(0.f, 0.f, 0.f);
     MediumRng mr = nee_medium_rng(key, bounce, k);
     Hit lrec;
-    bool hit = trace_shadow<COUNT, MEDIA>(s, p, ns.dir, 0.001f, PT_FLT_MAX, mr, lrec, counters);
+    bool hit = trace_shadow<COUNT, MEDIA>(s, p, ns.dir, 0.001f, PT_FLT_MAX, mr, lrec, counters, ns.known_inst, &ns.known);
     return nee_finish(s, ns, hit, lrec);
 }
 

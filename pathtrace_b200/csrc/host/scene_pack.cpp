@@ -63,13 +63,12 @@ PackedScene pack_scene(const FlatScene &f)
     if (n <= small_max) {
         out.small.resize(n);
         for (int i = 0; i < n; i++) {
-            pt::PtSmallEntry &e = out.small[i];
+            pt::PtBox &e = out.small[i];
             for (int k = 0; k < 3; k++) {
                 e.lo[k] = boxes[i].lo[k];
                 e.hi[k] = boxes[i].hi[k];
             }
             e.pad0 = e.pad1 = 0.f;
-            e.inst = out.inst[i];
         }
     }
     out.perlin_ranvec = f.perlin_ranvec;
@@ -101,6 +100,11 @@ pt::PtSceneView PackedScene::host_view(const FlatScene &f) const
     v.n_lights = (int)f.lights.size();
     v.background = f.background;
     v.n_media = n_media;
+    v.emit_needs_p = 0;
+    for (const b200pt_material &m : f.materials)
+        if (m.kind == B200PT_MAT_DIFFUSE_LIGHT &&
+            !(m.texture >= 0 && m.texture < (int)f.textures.size() && f.textures[m.texture].kind == B200PT_TEX_CONSTANT))
+            v.emit_needs_p = 1;
     v.cam.origin = to_v3(f.camera.origin);
     v.cam.lower_left = to_v3(f.camera.lower_left);
     v.cam.horizontal = to_v3(f.camera.horizontal);
