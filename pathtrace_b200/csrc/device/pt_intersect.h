@@ -137,6 +137,62 @@ PT_HD bool hit_box(const float *p, V3 o, V3 d, float t_min, float t_max, PrimHit
     return true;
 }
 
+// The two calls constant_medium::hit makes on a box boundary (volume.h:39-41): box::hit over (-inf, inf) -> ta, then
+// box::hit over (ta + 0.0001, inf) -> tb.  A side's t and its bound test do not depend on the range, so the six
+// sides are evaluated once and the list walk of hit_box (inclusive upper bound: a later side at the same t
+// replaces an earlier one) is replayed twice over the stored t's; only t is used by the medium.
+PT_HD bool box_entry_exit(const float *p, V3 o, V3 d, float &ta, float &tb)
+{
+    float oa = o.z, ob = o.x, oc = o.y, da = d.z, db = d.x, dc = d.y;
+    float la = p[2], lb = p[0], lc = p[1], ha = p[5], hb = p[3], hc = p[4];
+    float ts[6];
+    bool in[6];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int it = 0; it < 3; it++) {
+        float t = (la - oa) / da;
+        float bh = ob + t * db, ch = oc + t * dc;
+        ts[2 * it] = t;
+        in[2 * it] = !(bh < lb || bh > hb || ch < lc || ch > hc);
+        t = (ha - oa) / da;
+        bh = ob + t * db, ch = oc + t * dc;
+        ts[2 * it + 1] = t;
+        in[2 * it + 1] = !(bh < lb || bh > hb || ch < lc || ch > hc);
+        float r;
+        r = oa, oa = ob, ob = oc, oc = r;
+        r = da, da = db, db = dc, dc = r;
+        r = la, la = lb, lb = lc, lc = r;
+        r = ha, ha = hb, hb = hc, hc = r;
+    }
+    float closest = PT_FLT_MAX;
+    bool any = false;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int k = 0; k < 6; k++)
+        if (!(ts[k] < -PT_FLT_MAX || ts[k] > closest) && in[k]) { // NB a NaN t passes, as in rect::hit
+            closest = ts[k];
+            any = true;
+        }
+    if (!any)
+        return false;
+    ta = closest;
+    const float t_min = (float)((double)ta + 0.0001); // `rec1.t + 0.0001` is a double sum
+    closest = PT_FLT_MAX;
+    any = false;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int k = 0; k < 6; k++)
+        if (!(ts[k] < t_min || ts[k] > closest) && in[k]) {
+            closest = ts[k];
+            any = true;
+        }
+    tb = closest;
+    return any;
+}
+
 // the bare primitive (sphere | rect | box) in its local frame
 PT_HD bool hit_prim(uint32_t meta, const float *p, V3 o, V3 d, float t_min, float t_max, PrimHit &h)
 {
@@ -216,14 +272,13 @@ PT_HD bool hit_medium(uint32_t meta, const float *p, float density, V3 o, V3 d, 
             return false;
         if (!sphere_pick(r1, r2, (float)((double)ta + 0.0001), PT_FLT_MAX, tb)) // `rec1.t + 0.0001` is a double sum
             return false;
+    } else if (meta_kind(meta) == B200PT_PRIM_BOX) {
+        if (!box_entry_exit(p, o, d, ta, tb))
+            return false;
     } else {
-        PrimHit rec1, rec2;
-        if (!hit_prim(meta, p, o, d, -PT_FLT_MAX, PT_FLT_MAX, rec1))
-            return false;
-        if (!hit_prim(meta, p, o, d, (float)((double)rec1.t + 0.0001), PT_FLT_MAX, rec2))
-            return false;
-        ta = rec1.t;
-        tb = rec2.t;
+        // a rect boundary: the second boundary->hit starts 0.0001 behind the only crossing and finds nothing; a ray
+        // IN the plane gives t = NaN twice, and every comparison below is then false up to `hit_distance < NaN`
+        return false;
     }
     if (ta < t_min)
         ta = t_min;
