@@ -237,6 +237,8 @@ def ours_arm(args):
         raise SystemExit("bench.py: no CUDA device (this backend has no CPU fallback)")
     torch.cuda.set_device(local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # the version banner goes to stdout, which carries the ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():

@@ -244,6 +244,12 @@ int b200pt_render_profile(b200pt_render *render, b200pt_profile *out);
 
 void b200pt_render_destroy(b200pt_render *render);
 
+/* Device and pinned-host blocks of destroyed handles are kept for reuse by later handles (the reference `new`s
+ * everything once per process and never frees, main.cpp:108-168; a library that is called once per frame must not pay
+ * cudaMalloc for 1.3 GB of wavefront state every time).  This releases them.  Env B200PT_CACHE_MB caps the cache
+ * (default 8192, 0 = off). */
+void b200pt_trim_cache(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -101,6 +101,7 @@ SIGNATURES = {
     "b200pt_render_write_ppm": (C.c_int, [C.c_void_p, C.c_int64, C.c_char_p]),
     "b200pt_render_profile": (C.c_int, [C.c_void_p, C.POINTER(Profile)]),
     "b200pt_render_destroy": (None, [C.c_void_p]),
+    "b200pt_trim_cache": (None, []),
 }
 
 _lib = None

@@ -13,7 +13,12 @@
 #include <cstdio>
 #include <cstring>
 #include <fstream>
+#include <algorithm>
+#include <cstdlib>
+#include <map>
 #include <memory>
+#include <mutex>
+#include <thread>
 #include <sstream>
 #include <stdexcept>
 #include <string>
@@ -59,11 +64,158 @@ template <typename F> int guarded(F &&f)
     }
 }
 
-template <typename T> T *dev_upload(const std::vector<T> &v)
+// Device and pinned-host blocks of destroyed handles are kept for the next handle that asks for the same size: a
+// render allocates ~1.3 GB of wavefront state in 20 blocks, and cudaMalloc/cudaFree of those cost more than
+// rendering a few samples per pixel.  Blocks enter the cache only after the owning stream has been synchronised.
+// B200PT_CACHE_MB caps the cached device bytes (default 8192; 0 disables); b200pt_trim_cache() empties it.
+class BlockCache {
+  public:
+    void *dev_get(int device, size_t bytes)
+    {
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            auto it = dev_.find({device, bytes});
+            if (it != dev_.end()) {
+                void *p = it->second;
+                dev_.erase(it);
+                dev_bytes_ -= bytes;
+                return p;
+            }
+        }
+        void *p = nullptr;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e == cudaErrorMemoryAllocation) {
+            cudaGetLastError();
+            trim();
+            e = cudaMalloc(&p, bytes);
+        }
+        if (e != cudaSuccess)
+            throw CudaError(std::string("cudaMalloc: ") + cudaGetErrorString(e));
+        return p;
+    }
+    void dev_put(int device, void *p, size_t bytes)
+    {
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            if (dev_bytes_ + bytes <= cap()) {
+                dev_.insert({{device, bytes}, p});
+                dev_bytes_ += bytes;
+                return;
+            }
+        }
+        cudaFree(p);
+    }
+    void *pinned_get(size_t bytes)
+    {
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            auto it = pinned_.find(bytes);
+            if (it != pinned_.end()) {
+                void *p = it->second;
+                pinned_.erase(it);
+                pinned_bytes_ -= bytes;
+                return p;
+            }
+        }
+        void *p = nullptr;
+        CK(cudaHostAlloc(&p, bytes, cudaHostAllocDefault));
+        return p;
+    }
+    void pinned_put(void *p, size_t bytes)
+    {
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            if (pinned_bytes_ + bytes <= (cap() ? (size_t)1 << 30 : 0)) {
+                pinned_.insert({bytes, p});
+                pinned_bytes_ += bytes;
+                return;
+            }
+        }
+        cudaFreeHost(p);
+    }
+    void trim()
+    {
+        std::lock_guard<std::mutex> g(mu_);
+        int cur = 0;
+        cudaGetDevice(&cur);
+        for (auto &kv : dev_) {
+            cudaSetDevice(kv.first.first);
+            cudaFree(kv.second);
+        }
+        cudaSetDevice(cur);
+        for (auto &kv : pinned_)
+            cudaFreeHost(kv.second);
+        dev_.clear();
+        pinned_.clear();
+        dev_bytes_ = pinned_bytes_ = 0;
+    }
+
+  private:
+    static size_t cap()
+    {
+        static const size_t c = [] {
+            const char *e = std::getenv("B200PT_CACHE_MB");
+            return (size_t)(e ? std::max(0ll, atoll(e)) : 8192ll) << 20;
+        }();
+        return c;
+    }
+    std::mutex mu_;
+    std::multimap<std::pair<int, size_t>, void *> dev_;
+    std::multimap<size_t, void *> pinned_;
+    size_t dev_bytes_ = 0, pinned_bytes_ = 0;
+};
+
+// memcpy into caller memory that has often never been touched (a fresh numpy array): page faults dominate, and they
+// scale with threads
+void parallel_memcpy(void *dst, const void *src, size_t bytes)
+{
+    const size_t chunk = (size_t)4 << 20;
+    unsigned n = (unsigned)std::min<size_t>((bytes + chunk - 1) / chunk, std::min(8u, std::max(1u, std::thread::hardware_concurrency())));
+    if (n <= 1) {
+        memcpy(dst, src, bytes);
+        return;
+    }
+    std::vector<std::thread> pool;
+    const size_t per = ((bytes / n) + 4095) & ~(size_t)4095;
+    for (unsigned t = 0; t < n; t++) {
+        const size_t a = std::min(bytes, per * t), b = std::min(bytes, per * (t + 1));
+        if (b > a)
+            pool.emplace_back([=] { memcpy((char *)dst + a, (const char *)src + a, b - a); });
+    }
+    for (auto &th : pool)
+        th.join();
+}
+
+int sm_count(int device)
+{
+    static std::mutex mu;
+    static std::map<int, int> known;
+    std::lock_guard<std::mutex> g(mu);
+    auto it = known.find(device);
+    if (it != known.end())
+        return it->second;
+    int n = 0;
+    CK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device));
+    return known[device] = n;
+}
+
+BlockCache &block_cache()
+{
+    static BlockCache *c = new BlockCache; // leaked on purpose: no CUDA calls from static destructors
+    return *c;
+}
+
+struct DevBlock {
+    void *p;
+    size_t bytes;
+};
+
+template <typename T> T *dev_upload(const std::vector<T> &v, int device, std::vector<DevBlock> &owned)
 {
     T *d = nullptr;
     size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
-    CK(cudaMalloc(&d, bytes));
+    d = (T *)block_cache().dev_get(device, bytes);
+    owned.push_back({d, bytes});
     if (!v.empty())
         CK(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
     return d;
@@ -89,17 +241,19 @@ struct b200pt_scene {
     int device = 0;
     cudaStream_t stream = nullptr;
     pt::PtSceneView view{};
-    std::vector<void *> allocations;
+    std::vector<DevBlock> allocations;
     int n_media = 0;
 
     ~b200pt_scene()
     {
         if (device >= 0)
             cudaSetDevice(device);
-        for (void *p : allocations)
-            cudaFree(p);
-        if (stream)
+        if (stream) {
+            cudaStreamSynchronize(stream);
             cudaStreamDestroy(stream);
+        }
+        for (const DevBlock &b : allocations)
+            block_cache().dev_put(device, b.p, b.bytes);
     }
 };
 
@@ -114,21 +268,18 @@ void upload_scene(b200pt_scene &sc)
         return; // host-only handle: description and BVH can be inspected, nothing can be traced
     select_device(sc.device);
     CK(cudaStreamCreateWithFlags(&sc.stream, cudaStreamNonBlocking));
-    auto keep = [&](auto *p) {
-        sc.allocations.push_back((void *)p);
-        return p;
-    };
+    auto up = [&](const auto &vec) { return dev_upload(vec, sc.device, sc.allocations); };
     pt::PtSceneView &v = sc.view;
-    v.nodes = keep(dev_upload(sc.packed.bvh.nodes));
-    v.inst = keep(dev_upload(sc.packed.inst));
-    v.fwd = keep(dev_upload(sc.packed.fwd));
-    v.mats = keep(dev_upload(sc.flat.materials));
-    v.tex = keep(dev_upload(sc.flat.textures));
-    v.lights = keep(dev_upload(sc.flat.lights));
-    v.emitters = keep(dev_upload(sc.packed.emitters));
-    v.small = keep(dev_upload(sc.packed.small));
-    v.perlin_ranvec = keep(dev_upload(sc.packed.perlin_ranvec));
-    v.perlin_perm = keep(dev_upload(sc.packed.perlin_perm));
+    v.nodes = (up(sc.packed.bvh.nodes));
+    v.inst = (up(sc.packed.inst));
+    v.fwd = (up(sc.packed.fwd));
+    v.mats = (up(sc.flat.materials));
+    v.tex = (up(sc.flat.textures));
+    v.lights = (up(sc.flat.lights));
+    v.emitters = (up(sc.packed.emitters));
+    v.small = (up(sc.packed.small));
+    v.perlin_ranvec = (up(sc.packed.perlin_ranvec));
+    v.perlin_perm = (up(sc.packed.perlin_perm));
 }
 
 void need_device(const b200pt_scene *sc)
@@ -147,9 +298,10 @@ struct b200pt_render {
     pt::Wavefront wf{};
     pt::Film film{};
     pt::LaunchCfg lc{};
-    std::vector<void *> allocations;
+    std::vector<DevBlock> allocations;
     float *d_lum = nullptr;   // [2]
     uint8_t *d_rgb = nullptr; // H*W*3
+    float *d_rgbf = nullptr;  // H*W*3 floats: the film repacked for b200pt_render_read (allocated on first use)
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int batch_samples = 1;
     int batches_total = 0, batches_done = 0;
@@ -187,8 +339,10 @@ struct b200pt_render {
         }
         for (cudaEvent_t e : event_pool)
             cudaEventDestroy(e);
-        for (void *p : allocations)
-            cudaFree(p);
+        if (scene && scene->stream)
+            cudaStreamSynchronize(scene->stream); // nothing in flight may still touch a block that enters the cache
+        for (const DevBlock &b : allocations)
+            block_cache().dev_put(scene ? scene->device : 0, b.p, b.bytes);
         if (ev0)
             cudaEventDestroy(ev0);
         if (ev1)
@@ -200,11 +354,11 @@ namespace {
 
 template <typename T> T *render_alloc(b200pt_render &r, size_t count, bool zero = false)
 {
-    T *p = nullptr;
-    CK(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
-    r.allocations.push_back(p);
+    const size_t bytes = std::max<size_t>(count, 1) * sizeof(T);
+    T *p = (T *)block_cache().dev_get(r.scene->device, bytes);
+    r.allocations.push_back({p, bytes});
     if (zero)
-        CK(cudaMemset(p, 0, std::max<size_t>(count, 1) * sizeof(T)));
+        CK(cudaMemsetAsync(p, 0, bytes, r.scene->stream));
     return p;
 }
 
@@ -525,7 +679,8 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         ctl.nsamp = bs;
         ctl.remaining = c.samples - bs;
         ctl.batch_samples = bs;
-        CK(cudaMemcpy(wf.ctl, &ctl, sizeof(ctl), cudaMemcpyHostToDevice));
+        CK(cudaMemcpyAsync(wf.ctl, &ctl, sizeof(ctl), cudaMemcpyHostToDevice, scene->stream));
+        CK(cudaStreamSynchronize(scene->stream)); // `ctl` is a stack variable
 
         r->film.accum = render_alloc<float4>(*r, (size_t)npix, true);
         r->film.clamp = c.stats_clamp;
@@ -538,11 +693,9 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         CK(cudaEventCreate(&r->ev0));
         CK(cudaEventCreate(&r->ev1));
 
-        cudaDeviceProp prop;
-        CK(cudaGetDeviceProperties(&prop, scene->device));
         r->lc.threads = 256;
         r->lc.count_work = c.profile == 2;
-        r->lc.blocks = prop.multiProcessorCount * 8;
+        r->lc.blocks = sm_count(scene->device) * 8;
         *out = r.release();
     });
 }
@@ -591,15 +744,19 @@ int b200pt_render_read(b200pt_render *r, float *rgb_sums, int64_t *spp_done)
         return fail(B200PT_ERR_INVALID, "null argument");
     return guarded([&] {
         need_device(r->scene);
-        const size_t npix = (size_t)r->wf.npix;
-        std::vector<float4> tmp(npix);
-        CK(cudaMemcpyAsync(tmp.data(), r->film.accum, npix * sizeof(float4), cudaMemcpyDeviceToHost, r->scene->stream));
-        CK(cudaStreamSynchronize(r->scene->stream));
-        for (size_t i = 0; i < npix; i++) {
-            rgb_sums[3 * i + 0] = tmp[i].x;
-            rgb_sums[3 * i + 1] = tmp[i].y;
-            rgb_sums[3 * i + 2] = tmp[i].z;
-        }
+        // float4 sums -> packed rgb on the device, one D2H copy into pinned staging, one memcpy to the caller
+        const size_t npix = (size_t)r->wf.npix, bytes = npix * 3 * sizeof(float);
+        if (!r->d_rgbf)
+            r->d_rgbf = render_alloc<float>(*r, npix * 3);
+        pt::launch_pack_rgb(r->film.accum, (int)npix, r->d_rgbf, r->scene->stream);
+        void *stage = block_cache().pinned_get(bytes);
+        cudaError_t e = cudaMemcpyAsync(stage, r->d_rgbf, bytes, cudaMemcpyDeviceToHost, r->scene->stream);
+        if (e == cudaSuccess)
+            e = cudaStreamSynchronize(r->scene->stream);
+        if (e == cudaSuccess)
+            parallel_memcpy(rgb_sums, stage, bytes);
+        block_cache().pinned_put(stage, bytes);
+        CK(e);
         if (spp_done)
             *spp_done = r->spp_done;
     });
@@ -711,5 +868,7 @@ int b200pt_render_profile(b200pt_render *r, b200pt_profile *out)
 }
 
 void b200pt_render_destroy(b200pt_render *r) { delete r; }
+
+void b200pt_trim_cache(void) { block_cache().trim(); }
 
 } // extern "C"

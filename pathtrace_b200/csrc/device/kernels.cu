@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(kThreads) k_shade(PtSceneView s, RenderParams 
 // adjacent lanes: same origin, nearly the same target -> coherent traversal, and the sum is a fixed-order shuffle
 // reduction; otherwise float atomics.
 #ifndef PT_NEE_MEDIA_MINB
-#define PT_NEE_MEDIA_MINB 3
+#define PT_NEE_MEDIA_MINB 4
 #endif
 // ANY: the scene has at most PT_MAX_DIRECT_EMITTERS emitters -> emitters first, then an any-hit walk (trace_shadow)
 template <bool COUNT, bool MEDIA, bool ANY, bool SMALL>
@@ -555,6 +555,17 @@ __global__ void __launch_bounds__(kThreads) k_luminance(const float4 *__restrict
     }
 }
 
+// film sums float4 -> packed rgb floats (what b200pt_render_read hands to the caller)
+__global__ void __launch_bounds__(kThreads) k_pack_rgb(const float4 *__restrict__ accum, int npix, float *__restrict__ rgb)
+{
+    for (int i = blockIdx.x * kThreads + threadIdx.x; i < npix; i += gridDim.x * kThreads) {
+        float4 v = accum[i];
+        rgb[3 * (size_t)i + 0] = v.x;
+        rgb[3 * (size_t)i + 1] = v.y;
+        rgb[3 * (size_t)i + 2] = v.z;
+    }
+}
+
 __device__ __forceinline__ float uncharted2(float x)
 {
     // tonemap.h:4-15
@@ -692,6 +703,14 @@ void launch_luminance(const float4 *accum, int npix, float inv_n, float *max_tot
     if (blocks > 148 * 8)
         blocks = 148 * 8;
     k_luminance<<<blocks, kThreads, 0, st>>>(accum, npix, inv_n, max_total);
+}
+
+void launch_pack_rgb(const float4 *accum, int npix, float *rgb, cudaStream_t st)
+{
+    int blocks = (npix + kThreads - 1) / kThreads;
+    if (blocks > 148 * 8)
+        blocks = 148 * 8;
+    k_pack_rgb<<<blocks, kThreads, 0, st>>>(accum, npix, rgb);
 }
 
 void launch_tonemap(const float4 *accum, int width, int height, float inv_n, float exposure_mul, float max_lum,

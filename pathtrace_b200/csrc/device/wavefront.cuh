@@ -77,6 +77,7 @@ void launch_trace_batch(const PtSceneView &s, const float *rays, size_t n, const
 
 // film: luminance reduce (max, total of |sum/n|) and tonemap to bytes (top row first)
 void launch_luminance(const float4 *accum, int npix, float inv_n, float *max_total /* [2] */, cudaStream_t st);
+void launch_pack_rgb(const float4 *accum, int npix, float *rgb, cudaStream_t st);
 void launch_tonemap(const float4 *accum, int width, int height, float inv_n, float exposure_mul, float max_lum,
                     uint8_t *rgb, cudaStream_t st);
 
