@@ -61,6 +61,7 @@ extern "C" {
 #define B200PT_TEX_CONSTANT 0
 #define B200PT_TEX_CHECKER 1
 #define B200PT_TEX_PERLIN 2
+#define B200PT_TEX_IMAGE 3 /* image_texture (image.h:7-51): texel lookup by (u, v), with an alpha mask */
 
 typedef struct b200pt_instance {
     float fwd[12];      /* local->world 3x4 affine, row major (transform3.h:17-25) */
@@ -87,9 +88,16 @@ typedef struct b200pt_texture {
     float color[3];
     float alpha;
     float scale;  /* checker / perlin */
-    int32_t odd;  /* checker: texture ids */
+    int32_t odd;  /* checker: texture ids; image: index into images[] */
     int32_t even;
 } b200pt_texture;
+
+/* image_texture's storage (image.h:52-70): row y, column x at rgba[4 * (y * width + x)], components = byte / 255.0
+ * as from_4byte_vector computes them; row 0 is the FIRST row of the decoded file. */
+typedef struct b200pt_image {
+    int32_t width, height;
+    const float *rgba;
+} b200pt_image;
 
 typedef struct b200pt_camera { /* camera.h:9-36 */
     float origin[3], lower_left[3], horizontal[3], vertical[3], u[3], v[3], w[3];
@@ -110,6 +118,8 @@ typedef struct b200pt_scene_desc {
     /* Perlin tables (texture.h:180-183), 256 entries each; may be NULL when no perlin texture */
     const float *perlin_ranvec; /* 256 x 3 */
     const int32_t *perlin_perm; /* 3 x 256: x, y, z */
+    const b200pt_image *images; /* B200PT_TEX_IMAGE textures point here (texture.odd); may be NULL */
+    int32_t n_images;
 } b200pt_scene_desc;
 
 /* ---- render configuration: same keys as config.json (config.h:98-132) ------------------- */
@@ -161,6 +171,11 @@ int b200pt_config_from_json(const char *config_json, b200pt_config *out, char *s
  * host-only handle (no CUDA call): the compiled description and the BVH can be inspected, every call that would
  * trace returns B200PT_ERR_NO_DEVICE -- there is no CPU fallback. */
 int b200pt_scene_create_from_json(const char *scene_json, int32_t film_width, int32_t film_height, int32_t device,
+                                  b200pt_scene **out);
+/* Same, reading the scene file itself (main.cpp:119-121).  Relative "path" entries of png textures
+ * (scene_parser.h:318-323) are looked up in the working directory first, like the reference, then next to the scene
+ * file and in its parent directory. */
+int b200pt_scene_create_from_file(const char *scene_path, int32_t film_width, int32_t film_height, int32_t device,
                                   b200pt_scene **out);
 /* Same, from a caller-built flat description (copied). */
 int b200pt_scene_create(const b200pt_scene_desc *desc, int32_t device, b200pt_scene **out);

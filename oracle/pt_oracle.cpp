@@ -131,11 +131,12 @@ extern "C" {
 
 const char *pt_oracle_last_error(void) { return g_err.c_str(); }
 
-void *pt_oracle_scene_create(const char *scene_json, int film_w, int film_h)
+// asset_dir: where png textures are looked up after the working directory (may be null)
+void *pt_oracle_scene_create2(const char *scene_json, int film_w, int film_h, const char *asset_dir)
 {
     try {
         OracleScene *sc = new OracleScene;
-        sc->flat = compile_scene(Json::parse(scene_json), film_w, film_h);
+        sc->flat = compile_scene(Json::parse(scene_json), film_w, film_h, asset_dir ? asset_dir : "");
         sc->packed = pack_scene(sc->flat);
         sc->view = sc->packed.host_view(sc->flat);
         return sc;
@@ -143,6 +144,11 @@ void *pt_oracle_scene_create(const char *scene_json, int film_w, int film_h)
         g_err = e.what();
         return nullptr;
     }
+}
+
+void *pt_oracle_scene_create(const char *scene_json, int film_w, int film_h)
+{
+    return pt_oracle_scene_create2(scene_json, film_w, film_h, nullptr);
 }
 
 void pt_oracle_scene_destroy(void *scene) { delete (OracleScene *)scene; }

@@ -41,13 +41,18 @@ class Camera(C.Structure):
                 ("lens_radius", C.c_float)]
 
 
+class Image(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("rgba", C.POINTER(C.c_float))]
+
+
 class SceneDesc(C.Structure):
     _fields_ = [("instances", C.POINTER(Instance)), ("n_instances", C.c_int32),
                 ("materials", C.POINTER(Material)), ("n_materials", C.c_int32),
                 ("textures", C.POINTER(Texture)), ("n_textures", C.c_int32),
                 ("lights", C.POINTER(C.c_int32)), ("n_lights", C.c_int32),
                 ("background", C.c_int32), ("camera", Camera),
-                ("perlin_ranvec", C.POINTER(C.c_float)), ("perlin_perm", C.POINTER(C.c_int32))]
+                ("perlin_ranvec", C.POINTER(C.c_float)), ("perlin_perm", C.POINTER(C.c_int32)),
+                ("images", C.POINTER(Image)), ("n_images", C.c_int32)]
 
 
 class Config(C.Structure):
@@ -83,6 +88,7 @@ SIGNATURES = {
     "b200pt_version": (C.c_char_p, []),
     "b200pt_config_from_json": (C.c_int, [C.c_char_p, C.POINTER(Config), C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]),
     "b200pt_scene_create_from_json": (C.c_int, [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+    "b200pt_scene_create_from_file": (C.c_int, [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
     "b200pt_scene_create": (C.c_int, [C.POINTER(SceneDesc), C.c_int32, C.POINTER(C.c_void_p)]),
     "b200pt_scene_get_desc": (C.c_int, [C.c_void_p, C.POINTER(SceneDesc)]),
     "b200pt_scene_bvh_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_float)]),

@@ -277,6 +277,8 @@ void upload_scene(b200pt_scene &sc)
     v.tex = (up(sc.flat.textures));
     v.lights = (up(sc.flat.lights));
     v.emitters = (up(sc.packed.emitters));
+    v.images = (up(sc.packed.images));
+    v.texels = (up(sc.packed.texels));
     v.small = (up(sc.packed.small));
     v.perlin_ranvec = (up(sc.packed.perlin_ranvec));
     v.perlin_perm = (up(sc.packed.perlin_perm));
@@ -451,6 +453,29 @@ int b200pt_scene_create_from_json(const char *scene_json, int32_t film_width, in
         std::unique_ptr<b200pt_scene> sc(new b200pt_scene);
         sc->device = device;
         sc->flat = compile_scene(Json::parse(scene_json), film_width, film_height);
+        upload_scene(*sc);
+        *out = sc.release();
+    });
+}
+
+int b200pt_scene_create_from_file(const char *scene_path, int32_t film_width, int32_t film_height, int32_t device,
+                                  b200pt_scene **out)
+{
+    if (!scene_path || !out || film_width <= 0 || film_height <= 0)
+        return fail(B200PT_ERR_INVALID, "bad argument");
+    *out = nullptr;
+    return guarded([&] {
+        std::ifstream f(scene_path, std::ios::binary);
+        if (!f.good())
+            throw std::runtime_error(std::string("cannot open scene file '") + scene_path + "'");
+        std::stringstream ss;
+        ss << f.rdbuf();
+        const std::string path(scene_path);
+        const size_t slash = path.find_last_of('/');
+        const std::string dir = slash == std::string::npos ? std::string(".") : path.substr(0, slash);
+        std::unique_ptr<b200pt_scene> sc(new b200pt_scene);
+        sc->device = device;
+        sc->flat = compile_scene(Json::parse(ss.str().c_str()), film_width, film_height, dir);
         upload_scene(*sc);
         *out = sc.release();
     });

@@ -17,6 +17,7 @@ namespace pt {
 namespace {
 
 constexpr int kThreads = 256;
+constexpr int kFaceShift = 28; // hit_p.w = instance | box side << 28 (b200pt_scene_create refuses >= 2^28 instances)
 constexpr int kWarps = kThreads / 32;
 
 __device__ __forceinline__ V3 xyz(float4 a) { return v3(a.x, a.y, a.z); }
@@ -193,7 +194,7 @@ __global__ void __launch_bounds__(kExtThreads) k_extend(PtSceneView s, RenderPar
             Hit h;
             int kind = SK_MISS;
             if (T.template result<MEDIA>(s, h)) {
-                wf.hit_p[slot] = f4(h.p, __int_as_float(h.inst));
+                wf.hit_p[slot] = f4(h.p, __int_as_float(h.inst | (h.face << kFaceShift)));
                 wf.hit_n[slot] = f4(h.n, h.t);
                 kind = shade_kind_of(s.mats[meta_material(s.inst[h.inst].meta)].kind);
             }
@@ -239,11 +240,14 @@ __global__ void __launch_bounds__(kThreads) k_shade(PtSceneView s, RenderParams 
                 // only a light leaves `attenuation` as the previous vertex set it (material.h:187-191)
                 in.attenuation = kind == SK_LIGHT ? xyz(wf.att[slot]) : v3(0.f, 0.f, 0.f);
                 Hit rec;
-                rec.inst = __float_as_int(hp.w);
+                rec.inst = __float_as_int(hp.w) & ((1 << kFaceShift) - 1);
+                rec.face = __float_as_int(hp.w) >> kFaceShift;
                 rec.p = xyz(hp);
                 rec.n = xyz(hn);
                 rec.t = hn.w;
                 rec.u = rec.v = 0.f;
+                if (s.n_images > 0) // only image textures look at u, v
+                    hit_uv(s, rec.inst, rec.face, xyz(ro), xyz(rd), rec.t, rec.u, rec.v);
                 RngKey key = make_key(rp, wf, slot, sample_base);
                 F4 rnd = rng4(key, stage_word(bounce, RNG_SHADE, 0), 0);
                 PathVertexOut out;

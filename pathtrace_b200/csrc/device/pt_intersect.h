@@ -22,6 +22,7 @@ struct Hit {
     float t;
     V3 p, n;
     float u, v;
+    int face; // box: the side that was hit (see PrimHit); kept so that u, v can be recomputed later (hit_uv)
 };
 
 PT_HD V3 shuffle(V3 v, int plane)
@@ -375,6 +376,37 @@ PT_HD bool hit_aabb(const float *lo, const float *hi, V3 o, V3 inv_d, float t_mi
 // closest t so far, widened by ~3 ulps for the culling tests
 PT_HD float cull_limit(float best_t) { return best_t + fabsf(best_t) * 4e-7f; }
 
+// rec.u / rec.v: only rect::hit sets them (primitive.h:206-207; a box side is a rect); sphere and constant_medium
+// leave them as they were (Q11) -- reported as 0.  (lo, ld) = the ray in the instance's frame.
+template <bool MEDIA> PT_HD void local_uv(const InstanceData &I, V3 lo, V3 ld, float t, int face, float &u, float &v)
+{
+    u = v = 0.f;
+    if (MEDIA && meta_medium(I.meta))
+        return;
+    const int kind = meta_kind(I.meta);
+    const float *p = I.p;
+    if (kind == B200PT_PRIM_RECT) {
+        rect_uv(meta_plane(I.meta), p[0], p[1], p[2], p[3], lo, ld, t, u, v);
+    } else if (kind == B200PT_PRIM_BOX) {
+        const int f = face >> 1;
+        if (f == 0)
+            rect_uv(B200PT_PLANE_XY, p[0], p[1], p[3], p[4], lo, ld, t, u, v);
+        else if (f == 1)
+            rect_uv(B200PT_PLANE_YZ, p[1], p[2], p[4], p[5], lo, ld, t, u, v);
+        else
+            rect_uv(B200PT_PLANE_XZ, p[0], p[2], p[3], p[5], lo, ld, t, u, v);
+    }
+}
+
+// the same u, v from what the wavefront keeps of a hit (the ray, t, the instance and the box side): the shade
+// kernels call this only when the scene has image textures
+PT_HD void hit_uv(const PtSceneView &s, int inst, int face, V3 o, V3 d, float t, float &u, float &v)
+{
+    InstanceData I;
+    load_instance(s.inst, inst, I);
+    local_uv<true>(I, xform_point(I.inv, o), xform_vector(I.inv, d), t, face, u, v);
+}
+
 struct TraceCounters {
     uint32_t boxes, prims;
 };
@@ -645,6 +677,7 @@ struct Traversal {
             out.p = v3(0.f, 0.f, 0.f);
             out.n = eigen_normalized(xform_vector_transposed(I.inv, best.n));
             out.u = out.v = 0.f;
+            out.face = best.face;
             return true;
         }
         V3 lo = xform_point(I.inv, o);
@@ -657,22 +690,8 @@ struct Traversal {
         out.n = eigen_normalized(xform_vector_transposed(I.inv, best.n));
         // rec.u / rec.v: only rect::hit sets them (primitive.h:206-207; a box side is a rect); sphere and
         // constant_medium leave them as they were (Q11) -- reported as 0
-        out.u = out.v = 0.f;
-        if (!(MEDIA && meta_medium(I.meta))) {
-            const int kind = meta_kind(I.meta);
-            const float *p = I.p;
-            if (kind == B200PT_PRIM_RECT) {
-                rect_uv(meta_plane(I.meta), p[0], p[1], p[2], p[3], lo, ld, best.t, out.u, out.v);
-            } else if (kind == B200PT_PRIM_BOX) {
-                const int f = best.face >> 1;
-                if (f == 0)
-                    rect_uv(B200PT_PLANE_XY, p[0], p[1], p[3], p[4], lo, ld, best.t, out.u, out.v);
-                else if (f == 1)
-                    rect_uv(B200PT_PLANE_YZ, p[1], p[2], p[4], p[5], lo, ld, best.t, out.u, out.v);
-                else
-                    rect_uv(B200PT_PLANE_XZ, p[0], p[2], p[3], p[5], lo, ld, best.t, out.u, out.v);
-            }
-        }
+        out.face = best.face;
+        local_uv<MEDIA>(I, lo, ld, best.t, best.face, out.u, out.v);
         return true;
     }
 };

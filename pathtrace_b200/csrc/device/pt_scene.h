@@ -57,6 +57,18 @@ PT_HD uint32_t meta_medium_slot(uint32_t m) { return (m >> 8) & 0xffu; }
 PT_HD int meta_material(uint32_t m) { return (int)((m >> 16) & 0x7fffu); }
 PT_HD bool meta_emitter(uint32_t m) { return (m >> 31) & 1u; }
 
+// image_texture (image.h:7-51): texels of all images in one float4 array (rgb + alpha), row-major, first row of the
+// file first
+struct alignas(16) PtImage {
+    int32_t width, height;
+    uint32_t offset; // first texel in PtSceneView::texels
+    int32_t pad;
+};
+
+struct alignas(16) PtTexel {
+    float r, g, b, a;
+};
+
 struct PtCamera {
     V3 origin, lower_left, horizontal, vertical, u, v;
     float lens_radius;
@@ -71,9 +83,11 @@ struct PtSceneView {
     const int32_t *lights;
     const PtBox *small;         // n_small leaf boxes, index = instance index; n_small == 0: use the BVH
     const int32_t *emitters;    // instances whose hit material emits (shadow rays test these first, pt_intersect.h)
+    const PtImage *images;
+    const PtTexel *texels;
     const float *perlin_ranvec; // 256 x 3
     const int32_t *perlin_perm; // 3 x 256
-    int32_t n_nodes, n_inst, n_lights, n_emitters, n_small, background;
+    int32_t n_nodes, n_inst, n_lights, n_emitters, n_small, n_images, background;
     int32_t emit_needs_p; // some emitter has a non-constant texture: shadow hits must report p (else only the normal)
     int32_t n_media; // instances wrapped in a constant_medium; 0 selects the kernels compiled without that branch
     PtCamera cam;

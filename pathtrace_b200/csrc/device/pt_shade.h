@@ -45,10 +45,31 @@ PT_HD float perlin_noise(const PtSceneView &s, V3 p)
 }
 
 // texture::value and texture::alpha in one walk (checker textures may nest, texture.h:46-68)
-PT_HD void tex_eval(const PtSceneView &s, int id, V3 p, V3 &value, float &alpha)
+PT_HD void tex_eval(const PtSceneView &s, int id, float u, float v, V3 p, V3 &value, float &alpha)
 {
     for (int depth = 0; depth < 8; depth++) {
         const b200pt_texture &t = s.tex[id];
+        if (t.kind == B200PT_TEX_IMAGE) {
+            // image_texture::value / alpha (image.h:15-46): wrap by truncation, then nearest texel.  The reference
+            // indexes past the row for u == 1 or v == 1 exactly; clamped here.
+            // A NaN coordinate (a ray IN the rect's plane) is int(NaN) there, i.e. a crash; it reads texel 0 here.
+            const PtImage &im = s.images[t.odd];
+            u = is_nan(u) ? 0.f : u;
+            v = is_nan(v) ? 0.f : v;
+            v -= (float)(int)v;
+            if (v < 0)
+                v += 1;
+            u -= (float)(int)u;
+            if (u < 0)
+                u += 1;
+            int y = (int)(v * im.height), x = (int)(u * im.width);
+            y = y < 0 ? 0 : (y >= im.height ? im.height - 1 : y);
+            x = x < 0 ? 0 : (x >= im.width ? im.width - 1 : x);
+            const PtTexel tx = s.texels[im.offset + (uint32_t)y * (uint32_t)im.width + (uint32_t)x];
+            value = v3(tx.r, tx.g, tx.b);
+            alpha = tx.a;
+            return;
+        }
         if (t.kind == B200PT_TEX_CHECKER) {
             float sines = sinf(t.scale * p.x) * sinf(t.scale * p.y) * sinf(t.scale * p.z);
             id = sines > 0 ? t.odd : t.even;
@@ -72,7 +93,7 @@ PT_HD void tex_eval(const PtSceneView &s, int id, V3 p, V3 &value, float &alpha)
 
 // material::emitted: only diffuse_light overrides it (material.h:209-228); isotropic's 3-argument `emitted`
 // does not override the 5-argument virtual (material.h:263-266), so media never emit.
-PT_HD V3 mat_emitted(const PtSceneView &s, const b200pt_material &m, V3 ray_dir, V3 n, V3 p)
+PT_HD V3 mat_emitted(const PtSceneView &s, const b200pt_material &m, V3 ray_dir, V3 n, float u, float v, V3 p)
 {
     if (m.kind != B200PT_MAT_DIFFUSE_LIGHT)
         return v3(0.f, 0.f, 0.f);
@@ -80,7 +101,7 @@ PT_HD V3 mat_emitted(const PtSceneView &s, const b200pt_material &m, V3 ray_dir,
     if (!aligned || m.two_sided) {
         V3 value;
         float alpha;
-        tex_eval(s, m.texture, p, value, alpha);
+        tex_eval(s, m.texture, u, v, p, value, alpha);
         return (m.power * value) * alpha;
     }
     return v3(0.f, 0.f, 0.f);
@@ -88,14 +109,15 @@ PT_HD V3 mat_emitted(const PtSceneView &s, const b200pt_material &m, V3 ray_dir,
 
 // material::scatter: returns did_scatter; `attenuation` is left untouched by a light (material.h:187-191), so the
 // caller's value from the previous vertex survives (integrator.h:181,199).
-PT_HD bool mat_scatter(const PtSceneView &s, const b200pt_material &m, V3 ray_dir, V3 n, V3 p, V3 &attenuation)
+PT_HD bool mat_scatter(const PtSceneView &s, const b200pt_material &m, V3 ray_dir, V3 n, float u, float v, V3 p,
+                       V3 &attenuation)
 {
     switch (m.kind) {
     case B200PT_MAT_LAMBERTIAN: {
         if (dot(ray_dir, n) < 0) {
             V3 value;
             float alpha;
-            tex_eval(s, m.texture, p, value, alpha);
+            tex_eval(s, m.texture, u, v, p, value, alpha);
             attenuation = value * (1.0f / PT_PI_F);
         } else {
             attenuation = v3(0.f, 0.f, 0.f);
@@ -111,7 +133,7 @@ PT_HD bool mat_scatter(const PtSceneView &s, const b200pt_material &m, V3 ray_di
     case B200PT_MAT_ISOTROPIC: {
         V3 value;
         float alpha;
-        tex_eval(s, m.texture, p, value, alpha);
+        tex_eval(s, m.texture, u, v, p, value, alpha);
         attenuation = value; // no 1/4pi (material.h:259) (sic)
         return true;
     }
@@ -333,7 +355,7 @@ PT_HD V3 nee_finish(const PtSceneView &s, const NeeSample &ns, bool hit, const H
     if (!hit)
         return v3(0.f, 0.f, 0.f);
     const b200pt_material &lm = s.mats[meta_material(s.inst[lrec.inst].meta)];
-    V3 light_emission = mat_emitted(s, lm, ns.dir, lrec.n, lrec.p);
+    V3 light_emission = mat_emitted(s, lm, ns.dir, lrec.n, lrec.u, lrec.v, lrec.p);
     V3 c = ns.coef * light_emission;
     c = div_fast(c, ns.pick_pdf);
     if (is_nan(c))
@@ -392,9 +414,9 @@ PT_HD void shade_hit_ineept(const PtSceneView &s, const RenderParams &rp, const 
     out.cont = false;
     out.mat_kind = m.kind;
     V3 attenuation = in.attenuation;
-    bool did_scatter = mat_scatter(s, m, in.d, rec.n, rec.p, attenuation);
+    bool did_scatter = mat_scatter(s, m, in.d, rec.n, rec.u, rec.v, rec.p, attenuation);
     float cos_i = fabsf(dot(unit_vector(in.d), unit_vector(rec.n))); // cosine of the INCOMING ray (sic)
-    V3 hit_emission = mat_emitted(s, m, in.d, rec.n, rec.p);
+    V3 hit_emission = mat_emitted(s, m, in.d, rec.n, rec.u, rec.v, rec.p);
     if (squared_length(hit_emission) > 0.000001f) {
         if (in.last_bsdf_pdf <= 0) {
             out.add += in.beta * hit_emission;
@@ -451,10 +473,10 @@ PT_HD void shade_hit_rpt(const PtSceneView &s, const RenderParams &rp, const Pat
     out.cont = false;
     out.mat_kind = m.kind;
     out.W = v3(0.f, 0.f, 0.f);
-    V3 emitted = mat_emitted(s, m, in.d, rec.n, rec.p);
+    V3 emitted = mat_emitted(s, m, in.d, rec.n, rec.u, rec.v, rec.p);
     out.add = in.beta * emitted;
     V3 attenuation = in.attenuation;
-    if (depth < rp.max_bounces && mat_scatter(s, m, in.d, rec.n, rec.p, attenuation)) {
+    if (depth < rp.max_bounces && mat_scatter(s, m, in.d, rec.n, rec.u, rec.v, rec.p, attenuation)) {
         V3 beta = in.beta * attenuation;
         if (beta.x == 0.f && beta.y == 0.f && beta.z == 0.f)
             return;
@@ -472,7 +494,14 @@ PT_HD V3 shade_miss(const PtSceneView &s, V3 d, V3 beta)
 {
     V3 value;
     float alpha;
-    tex_eval(s, s.background, unit_vector(d), value, alpha);
+    const V3 ud = unit_vector(d);
+    float u = 0.f, v = 0.f;
+    if (s.n_images > 0) {
+        // integrator.h:67-68,329-330 with `#define TAU 2 * M_PI` (random.h:7): x / TAU is (x / 2) * M_PI (sic, Q10)
+        u = (float)((3.14159265358979323846 + (double)atan2f(ud.y, ud.x)) / 2 * 3.14159265358979323846);
+        v = (float)((double)acosf(ud.z) / 3.14159265358979323846);
+    }
+    tex_eval(s, s.background, u, v, ud, value, alpha);
     return beta * value;
 }
 

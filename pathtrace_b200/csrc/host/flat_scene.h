@@ -12,6 +12,11 @@ struct Aabb {
     float lo[3], hi[3];
 };
 
+struct ImageData { // image_texture (image.h:7-70)
+    int32_t width = 0, height = 0;
+    std::vector<float> rgba; // 4 * width * height
+};
+
 struct FlatScene {
     std::vector<b200pt_instance> instances;
     std::vector<b200pt_material> materials;
@@ -21,6 +26,8 @@ struct FlatScene {
     b200pt_camera camera{};
     std::vector<float> perlin_ranvec;  // 256*3 (always filled: cheap)
     std::vector<int32_t> perlin_perm;  // 3*256
+    std::vector<ImageData> images;     // B200PT_TEX_IMAGE textures refer to these by index (texture.odd)
+    mutable std::vector<b200pt_image> image_views; // desc() scratch: views into `images`
     std::vector<std::string> warnings; // parser warnings the reference prints to stdout
 
     b200pt_scene_desc desc() const;
@@ -28,7 +35,13 @@ struct FlatScene {
 };
 
 // build_scene (scene_parser.h:241-595) + setup_camera (main.cpp:86-104).  Throws std::runtime_error.
-FlatScene compile_scene(const Json &scene, int film_width, int film_height);
+// asset_dir: where relative "path" entries of png textures are looked up after the working directory (the reference
+// opens them relative to the working directory only, scene_parser.h:39-55); may be empty.
+FlatScene compile_scene(const Json &scene, int film_width, int film_height, const std::string &asset_dir = "");
+
+// 8/16-bit PNG (grey, grey+alpha, RGB, palette, RGBA; non-interlaced) -> RGBA8 like lodepng::decode's default.
+// Throws std::runtime_error.
+void decode_png_rgba8(const std::string &path, std::vector<unsigned char> &rgba, unsigned &width, unsigned &height);
 
 // camera::camera (camera.h:9-36) in the reference's float arithmetic.
 b200pt_camera make_camera(const float lookfrom[3], const float lookat[3], float vfov_deg, float aspect, float aperture,

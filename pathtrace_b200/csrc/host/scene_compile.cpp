@@ -32,6 +32,7 @@ struct Prim {
 
 struct Builder {
     FlatScene out;
+    std::string asset_dir;
     std::map<std::string, int> textures;
     std::map<std::string, std::pair<int, std::string>> materials; // id -> (index, type string)
     std::map<std::string, Prim> primitives;
@@ -150,7 +151,43 @@ void parse_textures(Builder &b, const Json &scene)
                 b.out.textures.push_back(t);
                 idx = (int)b.out.textures.size() - 1;
             } else if (type == "png") {
-                throw std::runtime_error("scene: 'png' image textures (image.h) are not supported by this backend yet");
+                // decode_into_texture + from_4byte_vector (scene_parser.h:39-55, image.h:52-70)
+                const std::string rel = data["path"].as_string();
+                std::vector<std::string> tries = {rel};
+                if (!b.asset_dir.empty() && !rel.empty() && rel[0] != '/') {
+                    tries.push_back(b.asset_dir + "/" + rel);
+                    tries.push_back(b.asset_dir + "/../" + rel);
+                }
+                std::vector<unsigned char> bytes;
+                unsigned w = 0, h = 0;
+                std::string err;
+                bool ok = false;
+                for (const std::string &path : tries) {
+                    try {
+                        decode_png_rgba8(path, bytes, w, h);
+                        ok = true;
+                        break;
+                    } catch (const std::exception &ex) {
+                        if (err.empty() || std::string(ex.what()).find("cannot open") == std::string::npos)
+                            err = ex.what();
+                    }
+                }
+                if (!ok) // the reference prints the decoder error and goes on with an empty image, which is UB
+                    throw std::runtime_error("scene: " + err);
+                ImageData img;
+                img.width = (int32_t)w;
+                img.height = (int32_t)h;
+                img.rgba.resize(bytes.size());
+                for (size_t k = 0; k < bytes.size(); k++)
+                    img.rgba[k] = (float)(bytes[k] / 255.0); // `image[..] / 255.0` assigned to a float
+                b.out.images.push_back(std::move(img));
+                b200pt_texture t{};
+                t.kind = B200PT_TEX_IMAGE;
+                t.alpha = 1.f;
+                t.odd = (int32_t)b.out.images.size() - 1;
+                t.even = -1;
+                b.out.textures.push_back(t);
+                idx = (int)b.out.textures.size() - 1;
             } else {
                 // "constant", and any unknown string: std::map::operator[] maps it to enum 0 = CONSTANT (scene.h:79)
                 float c[3];
@@ -601,9 +638,10 @@ void replay_reference_rng(FlatScene &scene)
         l = new_index[l];
 }
 
-FlatScene compile_scene(const Json &scene, int film_width, int film_height)
+FlatScene compile_scene(const Json &scene, int film_width, int film_height, const std::string &asset_dir)
 {
     Builder b;
+    b.asset_dir = asset_dir;
     parse_textures(b, scene);
     parse_materials(b, scene);
 
@@ -708,6 +746,11 @@ b200pt_scene_desc FlatScene::desc() const
     d.camera = camera;
     d.perlin_ranvec = perlin_ranvec.empty() ? nullptr : perlin_ranvec.data();
     d.perlin_perm = perlin_perm.empty() ? nullptr : perlin_perm.data();
+    image_views.clear();
+    for (const ImageData &im : images)
+        image_views.push_back(b200pt_image{im.width, im.height, im.rgba.data()});
+    d.images = image_views.empty() ? nullptr : image_views.data();
+    d.n_images = (int32_t)image_views.size();
     return d;
 }
 
@@ -729,6 +772,19 @@ FlatScene FlatScene::from_desc(const b200pt_scene_desc &d)
         s.perlin_ranvec.assign(d.perlin_ranvec, d.perlin_ranvec + 256 * 3);
     if (d.perlin_perm)
         s.perlin_perm.assign(d.perlin_perm, d.perlin_perm + 3 * 256);
+    for (int k = 0; d.images && k < d.n_images; k++) {
+        const b200pt_image &im = d.images[k];
+        if (im.width <= 0 || im.height <= 0 || !im.rgba)
+            throw std::runtime_error("scene desc: bad image");
+        ImageData img;
+        img.width = im.width;
+        img.height = im.height;
+        img.rgba.assign(im.rgba, im.rgba + (size_t)4 * im.width * im.height);
+        s.images.push_back(std::move(img));
+    }
+    for (const auto &t : s.textures)
+        if (t.kind == B200PT_TEX_IMAGE && (t.odd < 0 || t.odd >= (int)s.images.size()))
+            throw std::runtime_error("scene desc: image texture refers to an image out of range");
     for (const auto &i : s.instances) {
         if (i.material < 0 || i.material >= (int)s.materials.size())
             throw std::runtime_error("scene desc: instance material out of range");

@@ -16,6 +16,8 @@ PackedScene pack_scene(const FlatScene &f)
     const int n = (int)f.instances.size();
     if (n <= 0)
         throw std::runtime_error("scene has no instances");
+    if (n >= (1 << 28))
+        throw std::runtime_error("too many instances (28-bit instance index in the wavefront hit record)");
     if (f.materials.size() > 32767)
         throw std::runtime_error("too many materials (15-bit material index)");
     out.inst.resize(n);
@@ -55,6 +57,16 @@ PackedScene pack_scene(const FlatScene &f)
         boxes[i] = instance_bounds(src);
     }
     out.n_media = media;
+    for (const ImageData &im : f.images) {
+        pt::PtImage pi{};
+        pi.width = im.width;
+        pi.height = im.height;
+        pi.offset = (uint32_t)out.texels.size();
+        out.images.push_back(pi);
+        const size_t ntex = (size_t)im.width * im.height;
+        for (size_t k = 0; k < ntex; k++)
+            out.texels.push_back(pt::PtTexel{im.rgba[4 * k], im.rgba[4 * k + 1], im.rgba[4 * k + 2], im.rgba[4 * k + 3]});
+    }
     out.bvh = build_bvh(boxes);
     // B200PT_SMALL_MAX (tests, A/B): 0 forces the BVH path on small scenes too
     int small_max = PT_SMALL_MAX;
@@ -89,6 +101,9 @@ pt::PtSceneView PackedScene::host_view(const FlatScene &f) const
     v.mats = f.materials.data();
     v.tex = f.textures.data();
     v.lights = f.lights.data();
+    v.images = images.data();
+    v.texels = texels.data();
+    v.n_images = (int)images.size();
     v.emitters = emitters.data();
     v.small = small.data();
     v.n_small = (int)small.size();

@@ -15,6 +15,8 @@ struct PackedScene {
     std::vector<float> perlin_ranvec;  // 768
     std::vector<int32_t> perlin_perm;  // 768
     std::vector<pt::PtBox> small; // filled when the scene has <= PT_SMALL_MAX instances (B200PT_SMALL_MAX=0: never)
+    std::vector<pt::PtImage> images;     // image textures: dimensions + offset into texels
+    std::vector<pt::PtTexel> texels;
     std::vector<int32_t> emitters;     // instances whose hit material is a diffuse_light, ascending
     int n_media = 0;
     // a view whose pointers refer to THIS object's host vectors and to `flat`'s material/texture/light arrays

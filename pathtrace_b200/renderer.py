@@ -98,8 +98,9 @@ class Scene:
 
     @classmethod
     def from_file(cls, path, film_width, film_height, device=0):
-        with open(path) as f:
-            return cls.from_json(f.read(), film_width, film_height, device)
+        h = C.c_void_p()
+        check(lib().b200pt_scene_create_from_file(os.fspath(path).encode(), film_width, film_height, device, C.byref(h)))
+        return cls(h, device)
 
     @classmethod
     def from_desc(cls, desc, device=0):
@@ -144,6 +145,8 @@ class Scene:
         cam["lens_radius"] = d.camera.lens_radius
         out = {"instances": inst, "materials": mats, "textures": tex, "lights": [d.lights[i] for i in range(d.n_lights)],
                "background": d.background, "camera": cam}
+        out["images"] = [np.ctypeslib.as_array(d.images[i].rgba, shape=(d.images[i].height, d.images[i].width, 4)).copy()
+                         for i in range(d.n_images)]
         if d.perlin_ranvec:
             out["perlin_ranvec"] = np.ctypeslib.as_array(d.perlin_ranvec, shape=(256, 3)).copy()
             out["perlin_perm"] = np.ctypeslib.as_array(d.perlin_perm, shape=(3, 256)).copy()

@@ -217,7 +217,105 @@ def book2_final(seed=1234, n_instances=8192):
                  inst, textures)
 
 
+def cornell_box_image_textures():
+    """Not one of the reference's files: a Cornell box that exercises `png` textures (scene_parser.h:318-323,
+    image.h) on a lambertian back wall and box (rect u, v incl. the `v` quirk of primitive.h:207) and as the world
+    texture seen through the open front (integrator.h:325-335).  Paths are relative to the repository root, where
+    the reference harness runs.  The light keeps a constant texture: the reference itself cannot render an
+    image-textured rect light under NEE -- the shadow rays it fires from a point ON the light to the light lie in
+    its plane, t = 0/0 passes rect::hit and image_texture::value indexes with int(NaN) (segfault); every textured
+    rect here has x0 == z0, which keeps `v` in [0, 1] and away from the out-of-range row of image.h:26 as well.
+    tests/test_gpu_render.py renders the image-LIGHT variant against the CPU restatement only."""
+    textures = [{"id": "panel", "type": "png", "data": {"path": "scenes/assets/panel.png"}},
+                {"id": "sky", "type": "png", "data": {"path": "scenes/assets/sky.png"}}]
+    mats = [lambertian("green", [0.12, 0.85, 0.05]), lambertian("red", [0.95, 0.05, 0.05]),
+            lambertian("white", [0.73, 0.73, 0.73]),
+            {"id": "poster", "type": "lambertian", "data": {"texture": "panel"}},
+            light("light", [0.6, 0.6, 0.6])]
+    prims = [WHITE_WALL, dict(id="poster_wall", **rect("poster", [555, 555])), dict(id="box", **box("poster", [165, 165, 165]))]
+    inst = [ref("white_wall", translate=[277.5, 0.0, 277.5]),
+            ref("white_wall", rotate=[1.0, 0.0, 0.0], translate=[277.5, 555, 277.5]),
+            ref("poster_wall", rotate=[1.5, 0, 0], translate=[277.5, 277.5, 555]),
+            direct(rect("green", [555, 555], align="yz", flip=True), translate=[555, 277.5, 277.5]),
+            direct(rect("red", [555, 555], align="yz"), translate=[0, 277.5, 277.5]),
+            ref("box", translate=[212.5, 82.5, 147.5], rotate=[0.0, -0.1, 0.0]), TALL_BOX,
+            direct(rect("light", [240, 230]), translate=[273, 554.0, 171])]
+    sc = scene(camera([278.0, 278.0, -750.0], [278.0, 278.0, 0.0], 40.0, 10.0), [0.0, 0.0, 0.0], mats, prims, inst,
+               textures)
+    sc["world"] = {"texture": "sky"}
+    return sc
+
+
+def write_png(path, rgba, color_type):
+    """A small PNG writer (stdlib only): rgba is H x W x 4 uint8; color_type 6 = RGBA8, 2 = RGB8.  Rows cycle through
+    the five scanline filters so that a reader has to undo every one of them."""
+    import struct
+    import zlib
+    h, w, _ = rgba.shape
+    ch = 4 if color_type == 6 else 3
+    rows = rgba[:, :, :ch].astype(np.int32).reshape(h, w * ch)
+    raw = bytearray()
+    prev = np.zeros(w * ch, dtype=np.int32)
+    for y in range(h):
+        cur = rows[y]
+        a = np.concatenate([np.zeros(ch, np.int32), cur[:-ch]])
+        c = np.concatenate([np.zeros(ch, np.int32), prev[:-ch]])
+        f = y % 5
+        if f == 0:
+            out = cur
+        elif f == 1:
+            out = cur - a
+        elif f == 2:
+            out = cur - prev
+        elif f == 3:
+            out = cur - ((a + prev) >> 1)
+        else:
+            p = a + prev - c
+            pa, pb, pc = np.abs(p - a), np.abs(p - prev), np.abs(p - c)
+            pred = np.where((pa <= pb) & (pa <= pc), a, np.where(pb <= pc, prev, c))
+            out = cur - pred
+        raw.append(f)
+        raw += bytes((out & 255).astype(np.uint8))
+        prev = cur
+
+    def chunk(tag, body):
+        return struct.pack(">I", len(body)) + tag + body + struct.pack(">I", zlib.crc32(tag + body) & 0xffffffff)
+
+    data = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, color_type, 0, 0, 0))
+    data += chunk(b"IDAT", zlib.compress(bytes(raw), 9)) + chunk(b"IEND", b"")
+    with open(path, "wb") as f:
+        f.write(data)
+
+
+def write_assets(outdir):
+    os.makedirs(os.path.join(outdir, "assets"), exist_ok=True)
+    rng = np.random.Generator(np.random.PCG64(99))
+    # panel: 16 x 8 colour blocks with a soft random tint; alpha falls off towards the left edge, with two holes
+    h, w = 8, 16
+    yy, xx = np.mgrid[0:h, 0:w]
+    panel = np.zeros((h, w, 4), dtype=np.uint8)
+    panel[..., 0] = 40 + 200 * ((xx // 4) % 2)
+    panel[..., 1] = 60 + 180 * ((yy // 2) % 2)
+    panel[..., 2] = 255 - 12 * xx
+    panel[..., :3] = np.clip(panel[..., :3].astype(np.int32) + rng.integers(-20, 21, size=(h, w, 3)), 0, 255)
+    panel[..., 3] = np.clip(64 + 16 * xx, 0, 255)
+    panel[2, 5, 3] = 0
+    panel[6, 11, 3] = 0
+    write_png(os.path.join(outdir, "assets", "panel.png"), panel, 6)
+    # sky: 32 x 16 RGB gradient with a bright band
+    h, w = 16, 32
+    yy, xx = np.mgrid[0:h, 0:w]
+    sky = np.zeros((h, w, 4), dtype=np.uint8)
+    sky[..., 0] = 30 + 6 * xx
+    sky[..., 1] = 80 + 8 * yy
+    sky[..., 2] = 230 - 5 * yy
+    sky[5:7, :, :3] = 250
+    sky[..., 3] = 255
+    write_png(os.path.join(outdir, "assets", "sky.png"), sky, 2)
+
+
 SCENES = {
+    "cornell_box_image_textures": cornell_box_image_textures,
     "three_orbs": three_orbs,
     "cornell_box": cornell_box,
     "cornell_box_small_lights": cornell_box_small_lights,
@@ -234,7 +332,8 @@ def main():
         with open(os.path.join(outdir, name + ".json"), "w") as f:
             json.dump(fn(), f, separators=(",", ":"))
             f.write("\n")
-    print("wrote", ", ".join(SCENES))
+    write_assets(outdir)
+    print("wrote", ", ".join(SCENES), "+ assets/panel.png, assets/sky.png")
 
 
 if __name__ == "__main__":

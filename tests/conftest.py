@@ -15,7 +15,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 SCENE_FILES = ["three_orbs", "cornell_box", "cornell_box_small_lights", "cornell_box_with_volume",
-               "cornell_box_with_volume2", "light_test", "book2_final"]
+               "cornell_box_with_volume2", "light_test", "book2_final", "cornell_box_image_textures"]
 
 
 def pytest_configure(config):

@@ -28,7 +28,8 @@ import scene_match  # noqa: E402
 from oracle_lib import PortOracle, RefDriver  # noqa: E402
 
 SMALL = ["three_orbs", "cornell_box", "cornell_box_small_lights", "cornell_box_with_volume", "cornell_box_with_volume2",
-         "light_test"]
+         "light_test", "cornell_box_image_textures"]
+ONLY = os.environ.get("GOLDEN_ONLY", "")  # regenerate only the scenes / tags containing this substring
 ALL = SMALL + ["book2_final"]
 W, H = 32, 18
 
@@ -43,7 +44,7 @@ def flat_of(name, w=W, h=H):
 
 
 def make_scene_dumps():
-    for name in SMALL:
+    for name in [n for n in SMALL if ONLY in n]:
         dump = RefDriver.scene(scene_file(name), W, H)
         with open(os.path.join(HERE, f"scene_{name}.json"), "w") as f:
             json.dump(dump, f, separators=(",", ":"))
@@ -51,7 +52,7 @@ def make_scene_dumps():
 
 
 def make_hits():
-    for name in ALL:
+    for name in [n for n in ALL if ONLY in n]:
         sc = flat_of(name)
         flat = sc.describe()
         ref_scene = RefDriver.scene(scene_file(name), W, H)
@@ -79,12 +80,15 @@ COLOR_CASES = {
     "cornell_box_with_volume_b2": ("cornell_box_with_volume", 32, 32, 2048, 3.0, dict(max_bounces=2)),
     "light_test_b2": ("light_test", 32, 18, 2048, 3.0, dict(max_bounces=2)),
     "book2_final_b2": ("book2_final", 32, 18, 2048, 3.0, dict(max_bounces=2)),
+    "cornell_box_image_textures_b2": ("cornell_box_image_textures", 32, 32, 2048, 3.0, dict(max_bounces=2)),
 }
 
 
 def make_color():
     import pathtrace_b200 as pt
     for tag, (scene, w, h, n, clamp, over) in COLOR_CASES.items():
+        if ONLY not in tag:
+            continue
         cfgd = pt.default_config_dict(width=w, height=h, samples=n, scene=scene_file(scene), **over)
         out = RefDriver.color(cfgd, n, clamp)
         cfg_store = dict(cfgd, scene=f"scenes/{scene}.json")

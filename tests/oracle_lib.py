@@ -102,7 +102,7 @@ def make_cconfig(config_dict, **over):
 
 
 class PortOracle:
-    def __init__(self, scene_json_text, w, h):
+    def __init__(self, scene_json_text, w, h, asset_dir=None):
         self.lib = C.CDLL(PORT_LIB)
         self.lib.pt_oracle_scene_create.restype = C.c_void_p
         self.lib.pt_oracle_scene_create.argtypes = [C.c_char_p, C.c_int, C.c_int]
@@ -113,7 +113,10 @@ class PortOracle:
         self.lib.pt_oracle_emitters.argtypes = [C.c_void_p, C.c_void_p]
         self.lib.pt_oracle_render.argtypes = [C.c_void_p, C.POINTER(_CConfig), C.c_void_p, C.c_void_p, C.c_void_p,
                                               C.POINTER(C.c_int64), C.c_int, C.c_int64, C.c_int64]
-        self.h = self.lib.pt_oracle_scene_create(scene_json_text.encode(), w, h)
+        self.lib.pt_oracle_scene_create2.restype = C.c_void_p
+        self.lib.pt_oracle_scene_create2.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_char_p]
+        self.h = self.lib.pt_oracle_scene_create2(scene_json_text.encode(), w, h,
+                                                  asset_dir.encode() if asset_dir else None)
         if not self.h:
             raise RuntimeError("pt_oracle: " + self.lib.pt_oracle_last_error().decode())
         self.w, self.hgt = w, h
@@ -121,7 +124,7 @@ class PortOracle:
     @classmethod
     def from_file(cls, path, w, h):
         with open(path) as f:
-            return cls(f.read(), w, h)
+            return cls(f.read(), w, h, asset_dir=os.path.dirname(os.path.abspath(path)))
 
     def close(self):
         if self.h:

@@ -8,7 +8,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import scene_path
+from conftest import ROOT, scene_path
 from oracle_lib import PortOracle, make_cconfig
 
 pytestmark = pytest.mark.gpu
@@ -54,6 +54,8 @@ CASES = [
     ("three_orbs", dict(integrator_type="recursive path tracing", max_bounces=5)),
     ("cornell_box", dict(only_direct_illumination=True)),
     ("cornell_box", dict(max_bounces=1)),
+    ("cornell_box_image_textures", dict()),
+    ("cornell_box_image_textures", dict(integrator_type="recursive path tracing", max_bounces=3)),
 ]
 
 
@@ -70,6 +72,36 @@ def test_render_matches_cpu_restatement(scene, over):
     for k in ("rays_extension", "rays_shadow", "rays_reference"):
         assert abs(rep[k] - ref[k]) <= 2e-3 * ref[k] + 8, (k, rep[k], ref[k])
     assert rep["camera_rays"] == w * h * spp
+
+
+def test_image_textured_light_matches_cpu_restatement(tmp_path):
+    """The variant the reference cannot render (scenes/make_scenes.py: its NEE indexes the image with int(NaN)): the
+    light's emission AND alpha come from a png (material.h:209-228), shadow hits must then carry p, u, v
+    (PtSceneView::emit_needs_p).  GPU against the CPU restatement, sample for sample."""
+    with open(scene_path("cornell_box_image_textures")) as f:
+        sj = json.load(f)
+    for m in sj["materials"]:
+        if m["id"] == "light":
+            m["data"] = {"texture": "panel", "power": 3.0, "two_sided": True}
+    path = str(tmp_path / "image_light.json")
+    with open(path, "w") as f:
+        json.dump(sj, f)
+    import pathtrace_b200 as pt
+    w, h, spp = 48, 40, 6
+    cfgd = pt.default_config_dict(width=w, height=h, samples=spp, scene=path)
+    here = os.getcwd()
+    os.chdir(ROOT)  # "scenes/assets/panel.png" is relative to the repository root
+    try:
+        r, rep = _render(cfgd, batch_samples=4)
+        oracle = PortOracle.from_file(path, w, h)
+    finally:
+        os.chdir(here)
+    ref = oracle.render(make_cconfig(cfgd), stats=False)
+    fb = r.framebuffer
+    _close(fb, ref["sums"], "image light")
+    assert fb.max() > 0
+    plain = _render(_cfg("cornell_box_image_textures", w, h, spp), batch_samples=4)[0].framebuffer
+    assert not np.allclose(plain, fb)  # the textured light does change the picture
 
 
 def test_batching_and_sharding_invariance():
@@ -141,7 +173,7 @@ def test_tonemap_and_ppm(tmp_path):
 
 @pytest.mark.parametrize("tag", ["cornell_box_d1", "cornell_box_b3", "cornell_box_rpt", "three_orbs_full",
                                  "cornell_box_small_lights_d1", "cornell_box_with_volume_b2", "light_test_b2",
-                                 "book2_final_b2"])
+                                 "book2_final_b2", "cornell_box_image_textures_b2"])
 def test_render_matches_reference_golden(tag):
     """Statistical parity with the UNMODIFIED reference: golden per-pixel statistics of integrator->color made by
     tests/golden/make_golden.py (ref_driver `color` mode).  Clamped samples on both sides (finite variance)."""

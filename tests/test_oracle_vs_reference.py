@@ -64,7 +64,7 @@ def z_scores(mean_a, var_a, n_a, mean_b, var_b, n_b):
 
 
 COLOR_TAGS = ["cornell_box_d1", "cornell_box_b3", "cornell_box_rpt", "three_orbs_full", "cornell_box_small_lights_d1",
-              "cornell_box_with_volume_b2", "light_test_b2", "book2_final_b2"]
+              "cornell_box_with_volume_b2", "light_test_b2", "book2_final_b2", "cornell_box_image_textures_b2"]
 
 
 @pytest.mark.parametrize("tag", COLOR_TAGS)
