@@ -243,6 +243,7 @@ struct b200pt_scene {
     pt::PtSceneView view{};
     std::vector<DevBlock> allocations;
     int n_media = 0;
+    uint32_t shade_kinds = 1u << pt::SK_MISS; // shade queues that can ever be non-empty for this scene
 
     ~b200pt_scene()
     {
@@ -263,6 +264,14 @@ void upload_scene(b200pt_scene &sc)
 {
     sc.packed = pack_scene(sc.flat);
     sc.n_media = sc.packed.n_media;
+    for (const b200pt_instance &i : sc.flat.instances) {
+        switch (sc.flat.materials[i.material].kind) {
+        case B200PT_MAT_DIELECTRIC: sc.shade_kinds |= 1u << pt::SK_DIELECTRIC; break;
+        case B200PT_MAT_DIFFUSE_LIGHT: sc.shade_kinds |= 1u << pt::SK_LIGHT; break;
+        case B200PT_MAT_ISOTROPIC: sc.shade_kinds |= 1u << pt::SK_ISOTROPIC; break;
+        default: sc.shade_kinds |= 1u << pt::SK_DIFFUSE; break;
+        }
+    }
     sc.view = sc.packed.host_view(sc.flat); // host pointers, replaced below when a device is attached
     if (sc.device < 0)
         return; // host-only handle: description and BVH can be inspected, nothing can be traced
@@ -403,9 +412,12 @@ void enqueue_batch(b200pt_render &r)
     const int n_bounces = nee ? r.cfg.max_bounces : r.cfg.max_bounces + 1;
     for (int b = 0; b < n_bounces; b++) {
         launch_class(r, B200PT_K_EXTEND, 1, [&] { pt::launch_extend(s, r.rp, r.wf, b, r.lc, st); });
-        launch_class(r, B200PT_K_SHADE, pt::SK_COUNT, [&] {
+        // one launch per material kind the scene has (a queue of an absent kind stays empty)
+        const uint32_t kinds = r.scene->shade_kinds;
+        launch_class(r, B200PT_K_SHADE, __builtin_popcount(kinds), [&] {
             for (int k = 0; k < pt::SK_COUNT; k++)
-                pt::launch_shade(s, r.rp, r.wf, b, k, r.lc, st);
+                if (kinds & (1u << k))
+                    pt::launch_shade(s, r.rp, r.wf, b, k, r.lc, st);
         });
         if (nee)
             launch_class(r, B200PT_K_NEE, 1, [&] { pt::launch_nee(s, r.rp, r.wf, b, r.lc, st); });
