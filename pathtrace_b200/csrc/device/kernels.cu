@@ -211,7 +211,9 @@ __global__ void __launch_bounds__(kExtThreads) k_extend(PtSceneView s, RenderPar
         flush_counts(tc, nrays, wf.trace_counts);
 }
 
-__global__ void __launch_bounds__(kThreads) k_shade(PtSceneView s, RenderParams rp, Wavefront wf, int bounce, int kind)
+// One instantiation per (shade queue, integrator): each holds the code of its own materials only.
+template <int kind, bool NEE>
+__global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
     const long long sample_base = wf.ctl->sample_base;
     int32_t *row = wf.counters + bounce * CNT_ROW;
@@ -251,10 +253,10 @@ __global__ void __launch_bounds__(kThreads) k_shade(PtSceneView s, RenderParams 
                 RngKey key = make_key(rp, wf, slot, sample_base);
                 F4 rnd = rng4(key, stage_word(bounce, RNG_SHADE, 0), 0);
                 PathVertexOut out;
-                if (rp.integrator == B200PT_INTEGRATOR_INEEPT)
-                    shade_hit_ineept(s, rp, in, rec, rnd, out);
+                if (NEE)
+                    shade_hit_ineept<kind>(s, rp, in, rec, rnd, out);
                 else
-                    shade_hit_rpt(s, rp, in, rec, bounce, rnd, out);
+                    shade_hit_rpt<kind>(s, rp, in, rec, bounce, rnd, out);
                 if (out.add.x != 0.f || out.add.y != 0.f || out.add.z != 0.f)
                     wf.sum[slot] = make_float4(acc.x + out.add.x, acc.y + out.add.y, acc.z + out.add.z, 0.f);
                 if (out.want_nee) {
@@ -643,7 +645,22 @@ void launch_extend(const PtSceneView &s, const RenderParams &rp, const Wavefront
 void launch_shade(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, int kind,
                   const LaunchCfg &lc, cudaStream_t st)
 {
-    k_shade<<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce, kind);
+    const bool nee = rp.integrator == B200PT_INTEGRATOR_INEEPT;
+#define PT_LAUNCH_SHADE(K)                                                  \
+    case K:                                                                 \
+        if (nee)                                                            \
+            k_shade<K, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);  \
+        else                                                                \
+            k_shade<K, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce); \
+        break;
+    switch (kind) {
+        PT_LAUNCH_SHADE(SK_MISS)
+        PT_LAUNCH_SHADE(SK_DIFFUSE)
+        PT_LAUNCH_SHADE(SK_DIELECTRIC)
+        PT_LAUNCH_SHADE(SK_LIGHT)
+        PT_LAUNCH_SHADE(SK_ISOTROPIC)
+    }
+#undef PT_LAUNCH_SHADE
 }
 
 void launch_nee(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, const LaunchCfg &lc,

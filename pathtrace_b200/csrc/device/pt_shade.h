@@ -405,11 +405,30 @@ struct PathVertexOut {
     float last_bsdf_pdf;
 };
 
+// QUEUE: the shade queue the vertex came from (1 lambertian|metal, 2 dielectric, 3 diffuse_light, 4 isotropic --
+// ShadeKind in wavefront.cuh) or -1 when unknown (CPU restatement).  The kernels are instantiated per queue; telling
+// the compiler which materials can occur removes the other materials' code from each instance.
+template <int QUEUE> PT_HD void assume_queue(int mat_kind)
+{
+#if defined(__CUDA_ARCH__)
+    if (QUEUE == 1)
+        __builtin_assume(mat_kind == B200PT_MAT_LAMBERTIAN || mat_kind == B200PT_MAT_METAL);
+    if (QUEUE == 2)
+        __builtin_assume(mat_kind == B200PT_MAT_DIELECTRIC);
+    if (QUEUE == 3)
+        __builtin_assume(mat_kind == B200PT_MAT_DIFFUSE_LIGHT);
+    if (QUEUE == 4)
+        __builtin_assume(mat_kind == B200PT_MAT_ISOTROPIC);
+#endif
+}
+
+template <int QUEUE = -1>
 PT_HD void shade_hit_ineept(const PtSceneView &s, const RenderParams &rp, const PathVertexIn &in, const Hit &rec, F4 rnd,
                             PathVertexOut &out)
 {
     const uint32_t meta = s.inst[rec.inst].meta;
-    const b200pt_material &m = s.mats[meta_material(meta)];
+    const b200pt_material m = s.mats[meta_material(meta)]; // a copy: the assumption below sticks to the value
+    assume_queue<QUEUE>(m.kind);
     out.add = v3(0.f, 0.f, 0.f);
     out.cont = false;
     out.mat_kind = m.kind;
@@ -464,11 +483,13 @@ PT_HD void shade_hit_ineept(const PtSceneView &s, const RenderParams &rp, const 
 
 // RecursivePT::color unrolled: radiance = sum over vertices of (product of attenuations) * emitted
 // (integrator.h:29-72).  depth = index of this vertex (0 = first hit).
+template <int QUEUE = -1>
 PT_HD void shade_hit_rpt(const PtSceneView &s, const RenderParams &rp, const PathVertexIn &in, const Hit &rec, int depth,
                          F4 rnd, PathVertexOut &out)
 {
     const uint32_t meta = s.inst[rec.inst].meta;
-    const b200pt_material &m = s.mats[meta_material(meta)];
+    const b200pt_material m = s.mats[meta_material(meta)];
+    assume_queue<QUEUE>(m.kind);
     out.want_nee = false;
     out.cont = false;
     out.mat_kind = m.kind;
