@@ -149,6 +149,9 @@ typedef struct b200pt_config {
     int32_t profile;        /* measurement aid: 1 = bracket every kernel launch with CUDA events on the render stream
                                (per-kernel device time), 2 = run the traversal kernels with work counters on
                                (BVH boxes / primitives tested); see b200pt_render_profile.  0 in production. */
+    float trace_probability; /* config.h:122-131: should_trace_paths ? avg_number_of_paths / (samples * pixels) : 0.
+                                Each camera sample is recorded with this probability (renderer.h:652-668) */
+    int32_t trace_max_paths; /* capacity of the device-side path store; 0 = max(1024, 4 x the expected number) */
 } b200pt_config;
 
 typedef struct b200pt_scene b200pt_scene;
@@ -240,6 +243,19 @@ int b200pt_render_tonemap(b200pt_render *render, int64_t n_samples, uint8_t *rgb
                           float *avg_luminance);
 /* Writes "P6\nW H\n255\n" + payload (renderer.h:26-53). */
 int b200pt_render_write_ppm(b200pt_render *render, int64_t n_samples, const char *path);
+
+/* Traced paths (should_trace_paths; renderer.h:57-96,652-678, integrator.h:195-197): the hit point of every vertex of
+ * the recorded camera samples, kept on the device and ordered here by (sample, pixel).
+ * b200pt_render_paths: n_paths receives the number recorded; when the arrays are non-NULL up to `capacity` paths are
+ * copied: pixel[i], sample[i] (global sample index), length[i] (vertices), points[(i * stride + k) * 3 + c] with
+ * stride = *vertices_per_path.  b200pt_render_write_paths writes the reference's two text files
+ * (handle_traced_paths, renderer.h:57-96): "x,y,z" per vertex and a blank line per path; the same through
+ * camera::project (camera.h:49-109) as "x,y" -- with a trailing '!' where project() reports failure. */
+int b200pt_render_paths(b200pt_render *render, int32_t capacity, int32_t *n_paths, int32_t *vertices_per_path,
+                        int32_t *pixel, int64_t *sample, int32_t *length, float *points);
+int b200pt_render_write_paths(b200pt_render *render, const char *path_3d, const char *path_2d, int32_t *n_paths);
+/* The string value of a top-level key of config.json (e.g. "traced_paths_output_path"); empty when absent. */
+int b200pt_config_string(const char *config_json, const char *key, char *out, size_t cap);
 
 /* Per-kernel measurements of a render started with config.profile != 0. */
 #define B200PT_K_RAYGEN 0

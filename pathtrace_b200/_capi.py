@@ -62,7 +62,8 @@ class Config(C.Structure):
                 ("only_direct_illumination", C.c_int32), ("normal_offset", C.c_float),
                 ("block_width", C.c_int32), ("block_height", C.c_int32), ("threads", C.c_int32),
                 ("seed", C.c_uint64), ("sample_offset", C.c_int64), ("device", C.c_int32),
-                ("batch_samples", C.c_int32), ("stats_clamp", C.c_float), ("profile", C.c_int32)]
+                ("batch_samples", C.c_int32), ("stats_clamp", C.c_float), ("profile", C.c_int32),
+                ("trace_probability", C.c_float), ("trace_max_paths", C.c_int32)]
 
 
 class Progress(C.Structure):
@@ -105,6 +106,10 @@ SIGNATURES = {
     "b200pt_render_write": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
     "b200pt_render_tonemap": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "b200pt_render_write_ppm": (C.c_int, [C.c_void_p, C.c_int64, C.c_char_p]),
+    "b200pt_render_paths": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200pt_render_write_paths": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_int32)]),
+    "b200pt_config_string": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]),
     "b200pt_render_profile": (C.c_int, [C.c_void_p, C.POINTER(Profile)]),
     "b200pt_render_destroy": (None, [C.c_void_p]),
     "b200pt_trim_cache": (None, []),

@@ -719,6 +719,17 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         CK(cudaMemcpyAsync(wf.ctl, &ctl, sizeof(ctl), cudaMemcpyHostToDevice, scene->stream));
         CK(cudaStreamSynchronize(scene->stream)); // `ctl` is a stack variable
 
+        if (c.trace_probability > 0.f) {
+            // should_trace_paths (config.h:122-131): the expected number of recorded paths is avg_number_of_paths
+            const double expect = (double)c.trace_probability * (double)c.samples * (double)npix;
+            wf.path_max = c.trace_max_paths > 0 ? c.trace_max_paths : (int32_t)std::max(1024.0, std::min(4.0 * expect, 4.0e6));
+            wf.path_stride = c.max_bounces + 1;
+            wf.path_prob = c.trace_probability;
+            wf.path_id = render_alloc<int32_t>(*r, cap);
+            wf.path_hdr = render_alloc<int4>(*r, (size_t)wf.path_max, true);
+            wf.path_pts = render_alloc<float4>(*r, (size_t)wf.path_max * wf.path_stride, true);
+            wf.path_count = render_alloc<int32_t>(*r, 1, true);
+        }
         r->film.accum = render_alloc<float4>(*r, (size_t)npix, true);
         r->film.clamp = c.stats_clamp;
         if (c.stats_clamp > 0.f) {
@@ -887,6 +898,149 @@ int b200pt_render_write_ppm(b200pt_render *r, int64_t n_samples, const char *pat
     f << "P6\n" << r->cfg.width << " " << r->cfg.height << "\n255\n";
     f.write((const char *)rgb.data(), (std::streamsize)rgb.size());
     return f.good() ? B200PT_OK : fail(B200PT_ERR_INVALID, std::string("write failed: ") + path);
+}
+
+namespace {
+
+struct TracedPath {
+    int32_t pixel;
+    int64_t sample;
+    std::vector<float> pts; // 3 per vertex
+};
+
+// the device-side path store, ordered by (sample, pixel): the order does not depend on scheduling
+std::vector<TracedPath> fetch_paths(b200pt_render &r)
+{
+    std::vector<TracedPath> out;
+    if (!r.wf.path_id)
+        return out;
+    cudaStream_t st = r.scene->stream;
+    int32_t n = 0;
+    CK(cudaMemcpyAsync(&n, r.wf.path_count, sizeof(n), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    n = std::min(n, r.wf.path_max);
+    if (n <= 0)
+        return out;
+    const int stride = r.wf.path_stride;
+    std::vector<int4> hdr((size_t)n);
+    std::vector<float4> pts((size_t)n * stride);
+    CK(cudaMemcpyAsync(hdr.data(), r.wf.path_hdr, hdr.size() * sizeof(int4), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(pts.data(), r.wf.path_pts, pts.size() * sizeof(float4), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    out.resize((size_t)n);
+    for (int i = 0; i < n; i++) {
+        out[i].pixel = hdr[i].x;
+        out[i].sample = (int64_t)(uint32_t)hdr[i].y | ((int64_t)hdr[i].z << 32);
+        const int len = std::min(hdr[i].w, stride);
+        for (int k = 0; k < len; k++) {
+            const float4 &p = pts[(size_t)i * stride + k];
+            out[i].pts.insert(out[i].pts.end(), {p.x, p.y, p.z});
+        }
+    }
+    std::sort(out.begin(), out.end(), [](const TracedPath &a, const TracedPath &b) {
+        return a.sample != b.sample ? a.sample < b.sample : a.pixel < b.pixel;
+    });
+    return out;
+}
+
+// camera::project (camera.h:49-109), float arithmetic as written there
+bool camera_project(const b200pt_camera &c, const float pt[3], float &x, float &y)
+{
+    float d[3], a = 0.f, b = 0.f;
+    for (int k = 0; k < 3; k++) {
+        d[k] = c.origin[k] - pt[k];
+        a += (c.lower_left[k] - pt[k]) * c.w[k];
+    }
+    for (int k = 0; k < 3; k++)
+        b += d[k] * c.w[k];
+    const float t = a / b;
+    if (t < 0.0) {
+        const float lim = 1.0e+10f;
+        return !(fabsf(pt[0]) > lim || fabsf(pt[1]) > lim || fabsf(pt[2]) > lim);
+    }
+    float hp = 0.f, vp = 0.f, hh = 0.f, vv = 0.f;
+    for (int k = 0; k < 3; k++) {
+        const float p = pt[k] + t * d[k] - c.lower_left[k];
+        hp += c.horizontal[k] * p;
+        vp += c.vertical[k] * p;
+        hh += c.horizontal[k] * c.horizontal[k];
+        vv += c.vertical[k] * c.vertical[k];
+    }
+    x = hp / hh;
+    y = vp / vv;
+    return true;
+}
+
+} // namespace
+
+int b200pt_render_paths(b200pt_render *r, int32_t capacity, int32_t *n_paths, int32_t *vertices_per_path, int32_t *pixel,
+                        int64_t *sample, int32_t *length, float *points)
+{
+    if (!r || !n_paths)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    return guarded([&] {
+        need_device(r->scene);
+        std::vector<TracedPath> paths = fetch_paths(*r);
+        *n_paths = (int32_t)paths.size();
+        const int stride = r->wf.path_id ? r->wf.path_stride : 0;
+        if (vertices_per_path)
+            *vertices_per_path = stride;
+        for (int i = 0; i < (int)paths.size() && i < capacity; i++) {
+            if (pixel)
+                pixel[i] = paths[i].pixel;
+            if (sample)
+                sample[i] = paths[i].sample;
+            if (length)
+                length[i] = (int32_t)(paths[i].pts.size() / 3);
+            if (points)
+                std::copy(paths[i].pts.begin(), paths[i].pts.end(), points + (size_t)i * stride * 3);
+        }
+    });
+}
+
+int b200pt_render_write_paths(b200pt_render *r, const char *path_3d, const char *path_2d, int32_t *n_paths)
+{
+    if (!r || !path_3d || !path_2d)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    return guarded([&] {
+        need_device(r->scene);
+        std::vector<TracedPath> paths = fetch_paths(*r);
+        std::ofstream o3(path_3d), o2(path_2d);
+        if (!o3.good() || !o2.good())
+            throw std::runtime_error(std::string("cannot open ") + (o3.good() ? path_2d : path_3d));
+        const b200pt_camera &cam = r->scene->flat.camera;
+        int added = 0;
+        for (const TracedPath &p : paths) { // handle_traced_paths (renderer.h:57-96)
+            if (p.pts.empty())
+                continue;
+            added++;
+            for (size_t k = 0; k + 2 < p.pts.size(); k += 3) {
+                o3 << p.pts[k] << ',' << p.pts[k + 1] << ',' << p.pts[k + 2] << '\n';
+                float x = 0, y = 0;
+                const bool hit_scene = camera_project(cam, &p.pts[k], x, y);
+                if (0.0 < x && 0.0 < y && x <= 1.0 && y <= 1.0 && hit_scene)
+                    o2 << x << ',' << y << std::endl;
+                if (!hit_scene)
+                    o2 << x << ',' << y << '!' << std::endl;
+            }
+            o3 << std::endl;
+            o2 << std::endl;
+        }
+        if (n_paths)
+            *n_paths = added;
+    });
+}
+
+int b200pt_config_string(const char *config_json, const char *key, char *out, size_t cap)
+{
+    if (!config_json || !key || !out || !cap)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    return guarded([&] {
+        Json j = Json::parse(config_json);
+        std::string v = j.contains(key) && j[key].is_string() ? j[key].as_string() : std::string();
+        strncpy(out, v.c_str(), cap - 1);
+        out[cap - 1] = 0;
+    });
 }
 
 int b200pt_render_profile(b200pt_render *r, b200pt_profile *out)

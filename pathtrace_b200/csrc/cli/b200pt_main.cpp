@@ -40,7 +40,7 @@ int main(int argc, char *argv[])
         die("config");
     const long total_pixels = (long)config.width * config.height;
     const long min_camera_rays = (long)config.samples * total_pixels;
-    std::cout << "trace probability is " << 0.0 << std::endl;
+    std::cout << "trace probability is " << config.trace_probability << std::endl;
     std::cout << std::endl;
     std::cout << "config read complete, rendering image at " << config.width << "x" << config.height << "==" << total_pixels
               << "px^2" << std::endl;
@@ -98,6 +98,15 @@ int main(int argc, char *argv[])
     std::cout << "max lum " << max_lum << std::endl;
     if (b200pt_render_write_ppm(render, config.samples, ppm_path))
         die("write_ppm");
+    if (config.trace_probability > 0.f) { // handle_traced_paths (renderer.h:57-96)
+        char p3[1024], p2[1024];
+        int32_t added = 0;
+        if (b200pt_config_string(config_text.c_str(), "traced_paths_output_path", p3, sizeof(p3)) ||
+            b200pt_config_string(config_text.c_str(), "traced_paths_2d_output_path", p2, sizeof(p2)) ||
+            b200pt_render_write_paths(render, p3, p2, &added))
+            die("write_paths");
+        std::cout << "wrote " << added << " traced paths" << std::endl;
+    }
     b200pt_render_destroy(render);
     b200pt_scene_destroy(scene);
     return 0;

@@ -144,6 +144,19 @@ __global__ void __launch_bounds__(kThreads) k_raygen(PtSceneView s, RenderParams
         wf.beta[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
         wf.att[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
         wf.sum[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (wf.path_id) { // `random_double() < trace_probability` (renderer.h:652)
+            int id = -1;
+            if (rng4(key, stage_word(0, RNG_PATH_TRACE, 0), 0).x < wf.path_prob) {
+                id = atomicAdd(wf.path_count, 1);
+                if (id < wf.path_max) {
+                    const long long gs = sample_base + (long long)(key.sample - (uint32_t)sample_base);
+                    wf.path_hdr[id] = make_int4((int)key.pixel, (int)(gs & 0xffffffffll), (int)(gs >> 32), 0);
+                } else {
+                    id = -1;
+                }
+            }
+            wf.path_id[slot] = id;
+        }
     }
 }
 
@@ -250,6 +263,13 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
                 rec.u = rec.v = 0.f;
                 if (s.n_images > 0) // only image textures look at u, v
                     hit_uv(s, rec.inst, rec.face, xyz(ro), xyz(rd), rec.t, rec.u, rec.v);
+                if (wf.path_id) { // `_path->push_back(rec.p)` (integrator.h:34-37,195-198)
+                    const int id = wf.path_id[slot];
+                    if (id >= 0 && bounce < wf.path_stride) {
+                        wf.path_pts[(size_t)id * wf.path_stride + bounce] = f4(rec.p, 0.f);
+                        wf.path_hdr[id].w = bounce + 1;
+                    }
+                }
                 RngKey key = make_key(rp, wf, slot, sample_base);
                 F4 rnd = rng4(key, stage_word(bounce, RNG_SHADE, 0), 0);
                 PathVertexOut out;

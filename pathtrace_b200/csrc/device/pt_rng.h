@@ -53,6 +53,7 @@ enum {
     RNG_SHADE = 2,       // idx 0: {r1, r2, r3, russian roulette}
     RNG_NEE = 3,         // k = light sample: {light pick, s1, s2}
     RNG_NEE_MEDIUM = 4,  // k = light sample, idx = medium slot
+    RNG_PATH_TRACE = 6,  // idx 0: {record this camera sample? (renderer.h:652)}
     RNG_BATCH_MEDIUM = 5 // b200pt_trace_batch without explicit variates: (ray lo, ray hi) as (pixel, sample)
 };
 

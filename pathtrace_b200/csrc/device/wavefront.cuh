@@ -43,6 +43,14 @@ struct Wavefront {
     int32_t *q_nee;
     int32_t *counters; // (max_bounces + 2) rows of CNT_ROW
     BatchCtl *ctl;
+    // traced paths (config.trace_probability > 0, else null): slot -> path id, per path {pixel, sample lo, sample hi,
+    // vertices} and path_stride hit points
+    int32_t *path_id;
+    int4 *path_hdr;
+    float4 *path_pts;
+    int32_t *path_count;
+    int32_t path_max, path_stride;
+    float path_prob;
     unsigned long long *trace_counts; // profile == 2: {ext rays, boxes, prims, nee rays, boxes, prims}
     int32_t npix;
     int32_t capacity; // slots

@@ -59,6 +59,11 @@ ParsedConfig parse_config(const Json &j)
     c.device = (int32_t)j.value("device", 0);
     c.batch_samples = (int32_t)j.value("batch_samples", 0);
     out.device_count = (int32_t)j.value("device_count", 1);
+    // config.h:122-131: `long min_camera_rays = samples * film.total_pixels`
+    c.trace_probability = 0.f;
+    if (out.should_trace_paths)
+        c.trace_probability = (float)(j.value("avg_number_of_paths", 100.0) / (double)((long)c.samples * ((long)c.width * c.height)));
+    c.trace_max_paths = (int32_t)j.value("trace_max_paths", 0);
 
     if (c.width <= 0 || c.height <= 0)
         throw std::runtime_error("config: film size must be positive");

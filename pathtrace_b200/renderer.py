@@ -28,10 +28,13 @@ from ._capi import B200ptError, Config as _CConfig, check, lib
 class Config:
     """config.json -> render configuration (same keys and defaults as config.h:98-132)."""
 
-    def __init__(self, cconfig, scene_path="", ppm_output_path="out.ppm"):
+    def __init__(self, cconfig, scene_path="", ppm_output_path="out.ppm", traced_paths_output_path="",
+                 traced_paths_2d_output_path=""):
         self.c = cconfig
         self.scene_path = scene_path
         self.ppm_output_path = ppm_output_path
+        self.traced_paths_output_path = traced_paths_output_path
+        self.traced_paths_2d_output_path = traced_paths_2d_output_path
 
     @classmethod
     def from_json(cls, text):
@@ -41,7 +44,12 @@ class Config:
         scene = C.create_string_buffer(1024)
         ppm = C.create_string_buffer(1024)
         check(lib().b200pt_config_from_json(text.encode(), C.byref(c), scene, 1024, ppm, 1024))
-        return cls(c, scene.value.decode(), ppm.value.decode())
+        extra = []
+        for key in ("traced_paths_output_path", "traced_paths_2d_output_path"):
+            buf = C.create_string_buffer(1024)
+            check(lib().b200pt_config_string(text.encode(), key.encode(), buf, 1024))
+            extra.append(buf.value.decode())
+        return cls(c, scene.value.decode(), ppm.value.decode(), *extra)
 
     @classmethod
     def from_file(cls, path="config.json"):
@@ -56,7 +64,8 @@ class Config:
         C.memmove(C.byref(c), C.byref(self.c), C.sizeof(c))
         for k, v in kw.items():
             setattr(c, k, v)
-        return Config(c, self.scene_path, self.ppm_output_path)
+        return Config(c, self.scene_path, self.ppm_output_path, self.traced_paths_output_path,
+                      self.traced_paths_2d_output_path)
 
 
 def default_config_dict(**over):
@@ -291,6 +300,34 @@ class Wavefront:
         check(lib().b200pt_render_write_ppm(self._h, n, path.encode()))
 
 
+    def paths(self):
+        """Traced paths (should_trace_paths, renderer.h:652-678): a list of dicts {pixel, sample, points (k x 3)},
+        ordered by (sample, pixel)."""
+        n, stride = C.c_int32(), C.c_int32()
+        check(lib().b200pt_render_paths(self._h, 0, C.byref(n), C.byref(stride), None, None, None, None))
+        if n.value == 0:
+            return []
+        pixel = np.zeros(n.value, dtype=np.int32)
+        sample = np.zeros(n.value, dtype=np.int64)
+        length = np.zeros(n.value, dtype=np.int32)
+        pts = np.zeros((n.value, max(1, stride.value), 3), dtype=np.float32)
+        check(lib().b200pt_render_paths(self._h, n.value, C.byref(n), C.byref(stride), pixel.ctypes.data,
+                                        sample.ctypes.data, length.ctypes.data, pts.ctypes.data))
+        return [{"pixel": int(pixel[i]), "sample": int(sample[i]), "points": pts[i, :length[i]].copy()}
+                for i in range(len(pixel))]
+
+    def write_paths(self, path_3d=None, path_2d=None):
+        """handle_traced_paths (renderer.h:57-96): the two text files; returns the number of paths written."""
+        path_3d = path_3d or self.config.traced_paths_output_path
+        path_2d = path_2d or self.config.traced_paths_2d_output_path
+        for p in (path_3d, path_2d):
+            if os.path.dirname(p):
+                os.makedirs(os.path.dirname(p), exist_ok=True)
+        n = C.c_int32()
+        check(lib().b200pt_render_write_paths(self._h, path_3d.encode(), path_2d.encode(), C.byref(n)))
+        return n.value
+
+
 def renderer_from_config(scene, config):
     """main.cpp:57-84: every render_type of the reference maps onto the one wavefront scheduler."""
     return Wavefront(scene, config)
@@ -303,4 +340,6 @@ def render_file(config_path="config.json", device=0):
     scene = Scene.from_file(cfg.scene_path, cfg.width, cfg.height, device)
     r = renderer_from_config(scene, cfg).start_render()
     report = r.finalize(cfg.ppm_output_path)
+    if cfg.trace_probability > 0:
+        report["traced_paths"] = r.write_paths()
     return r, report

@@ -74,7 +74,8 @@ class _CConfig(C.Structure):  # mirrors b200pt_config (include/b200pt.h)
                 ("only_direct_illumination", C.c_int32), ("normal_offset", C.c_float),
                 ("block_width", C.c_int32), ("block_height", C.c_int32), ("threads", C.c_int32),
                 ("seed", C.c_uint64), ("sample_offset", C.c_int64), ("device", C.c_int32),
-                ("batch_samples", C.c_int32), ("stats_clamp", C.c_float), ("profile", C.c_int32)]
+                ("batch_samples", C.c_int32), ("stats_clamp", C.c_float), ("profile", C.c_int32),
+                ("trace_probability", C.c_float), ("trace_max_paths", C.c_int32)]
 
 
 INTEGRATORS = {"iterative nee path tracing": 4, "recursive path tracing": 0}
