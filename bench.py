@@ -274,6 +274,11 @@ def ours_arm(args):
     for _ in range(W):
         r.sync_progress(batches_per_step)
     film = ptd.film_tensor(r)
+    if world > 1:  # warm-up of the one collective: same size, scratch buffer (the first NCCL reduce sets up channels)
+        scratch = torch.zeros_like(film)
+        for _ in range(2):
+            ptd.reduce_film(scratch, 0)
+        del scratch
     launches0 = sum(r.profile()["launches"].values())
     p0 = r.progress
     t_dev0, paths0, rays0 = p0.seconds, p0.samples_done, p0.rays_extension + p0.rays_shadow
