@@ -64,7 +64,7 @@ PT_HD bool hit_rect(int plane, bool flip, float x0, float z0, float x1, float z1
 {
     V3 to = shuffle(o, plane);
     V3 td = shuffle(d, plane);
-    float t = (y - to.y) / td.y;
+    float t = fdiv(y - to.y, td.y);
     if (t < t0 || t > t1) // NB a NaN t passes, as in the reference
         return false;
     float xh = to.x + t * td.x;
@@ -106,7 +106,7 @@ PT_HD bool hit_box(const float *p, V3 o, V3 d, float t_min, float t_max, PrimHit
 #pragma unroll 1
 #endif
     for (int it = 0; it < 3; it++) {
-        float t = (la - oa) / da;
+        float t = fdiv(la - oa, da);
         if (!(t < t_min || t > closest)) { // NB a NaN t passes, as in the reference
             float bh = ob + t * db, ch = oc + t * dc;
             if (!(bh < lb || bh > hb || ch < lc || ch > hc)) {
@@ -115,7 +115,7 @@ PT_HD bool hit_box(const float *p, V3 o, V3 d, float t_min, float t_max, PrimHit
                 nsign = da < 0 ? 1.f : -1.f; // normal -e_a, turned to face the ray (primitive.h:214-222)
             }
         }
-        t = (ha - oa) / da;
+        t = fdiv(ha - oa, da);
         if (!(t < t_min || t > closest)) {
             float bh = ob + t * db, ch = oc + t * dc;
             if (!(bh < lb || bh > hb || ch < lc || ch > hc)) {
@@ -152,11 +152,11 @@ PT_HD bool box_entry_exit(const float *p, V3 o, V3 d, float &ta, float &tb)
 #pragma unroll
 #endif
     for (int it = 0; it < 3; it++) {
-        float t = (la - oa) / da;
+        float t = fdiv(la - oa, da);
         float bh = ob + t * db, ch = oc + t * dc;
         ts[2 * it] = t;
         in[2 * it] = !(bh < lb || bh > hb || ch < lc || ch > hc);
-        t = (ha - oa) / da;
+        t = fdiv(ha - oa, da);
         bh = ob + t * db, ch = oc + t * dc;
         ts[2 * it + 1] = t;
         in[2 * it + 1] = !(bh < lb || bh > hb || ch < lc || ch > hc);
@@ -593,7 +593,7 @@ struct Traversal {
                 const float *row = E.inv + (plane == B200PT_PLANE_XY ? 8 : (plane == B200PT_PLANE_YZ ? 0 : 4));
                 const float oy = row[0] * o.x + row[1] * o.y + row[2] * o.z + row[3]; // xform_point, that row
                 const float dy = row[0] * d.x + row[1] * d.y + row[2] * d.z;          // xform_vector, that row
-                const float t = (E.p[4] - oy) / dy;
+                const float t = fdiv(E.p[4] - oy, dy);
                 if (t < t_min || t > best_t) // rect::hit's own range test (a NaN t passes)
                     continue;
                 ok = hit_rect(plane, meta_flip(meta), E.p[0], E.p[1], E.p[2], E.p[3], E.p[4],
@@ -657,6 +657,23 @@ struct Traversal {
                 if (active && cur < 0)
                     active = leaf_step<COUNT, MEDIA, ANY>(s, mr, counters);
             }
+        }
+    }
+#endif
+
+#if defined(__CUDACC__)
+    // while-while: inner nodes until no lane of the warp wants one any more, then the leaves that were reached,
+    // together.  Same per-ray sequence of steps as run().
+    template <bool COUNT, bool MEDIA, bool ANY = false>
+    __device__ __forceinline__ void run_warp_nodes_first(const PtSceneView &s, bool active, const MediumRng &mr,
+                                                         TraceCounters *counters)
+    {
+        while (__any_sync(0xffffffffu, active)) {
+            while (__any_sync(0xffffffffu, active && cur >= 0))
+                if (active && cur >= 0)
+                    active = node_step<COUNT>(s, counters);
+            if (active) // cur < 0 here
+                active = leaf_step<COUNT, MEDIA, ANY>(s, mr, counters);
         }
     }
 #endif

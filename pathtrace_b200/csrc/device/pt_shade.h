@@ -18,7 +18,7 @@ struct RenderParams {
 
 // ---- textures (texture.h) ---------------------------------------------------------------------------------------
 
-PT_HD float perlin_noise(const PtSceneView &s, V3 p)
+PT_HD_COLD float perlin_noise(const PtSceneView &s, V3 p)
 {
     // perlin::noise (texture.h:132-156) + perlin_interp (texture.h:111-130): the smoothstep is applied twice (sic)
     float fx = floorf(p.x), fy = floorf(p.y), fz = floorf(p.z);
@@ -44,9 +44,14 @@ PT_HD float perlin_noise(const PtSceneView &s, V3 p)
     return accum;
 }
 
+PT_HD_COLD float checker_sines(float scale, V3 p) { return sinf(scale * p.x) * sinf(scale * p.y) * sinf(scale * p.z); }
+
 // texture::value and texture::alpha in one walk (checker textures may nest, texture.h:46-68)
 PT_HD void tex_eval(const PtSceneView &s, int id, float u, float v, V3 p, V3 &value, float &alpha)
 {
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1 // unrolled, the three sinf of a checker level are 1700 instructions in every kernel that shades
+#endif
     for (int depth = 0; depth < 8; depth++) {
         const b200pt_texture &t = s.tex[id];
         if (t.kind == B200PT_TEX_IMAGE) {
@@ -71,7 +76,7 @@ PT_HD void tex_eval(const PtSceneView &s, int id, float u, float v, V3 p, V3 &va
             return;
         }
         if (t.kind == B200PT_TEX_CHECKER) {
-            float sines = sinf(t.scale * p.x) * sinf(t.scale * p.y) * sinf(t.scale * p.z);
+            float sines = checker_sines(t.scale, p);
             id = sines > 0 ? t.odd : t.even;
             continue;
         }
@@ -231,6 +236,18 @@ PT_HD V3 mat_generate(const b200pt_material &m, V3 ray_dir, V3 n, float r1, floa
 
 // ---- lights (hittable::random / pdf_value through the instance wrapper, primitive.h:319-342) ------------------
 
+// sphere::random (primitive.h:51-58) + random_to_sphere (random.h:46-55)
+PT_HD_COLD V3 sphere_random(V3 center, float radius, V3 lo, float r1, float r2)
+{
+    V3 direction = center - lo;
+    float distance_squared = squared_length(direction);
+    Onb uvw = onb_from_w(direction);
+    float z = 1 + r2 * (sqrtf(1 - radius * radius / distance_squared) - 1);
+    float phi = 2 * PT_PI_F * r1;
+    float sq = sqrtf(1 - z * z);
+    return onb_local(uvw, v3(cosf(phi) * sq, sinf(phi) * sq, z));
+}
+
 PT_HD V3 light_random(const InstanceData &I, const float *fwd, V3 o, float r1, float r2)
 {
     V3 lo = xform_point(I.inv, o);
@@ -243,16 +260,7 @@ PT_HD V3 light_random(const InstanceData &I, const float *fwd, V3 o, float r1, f
         V3 pt = shuffle(v3(I.p[0] + r1 * (I.p[2] - I.p[0]), I.p[4], I.p[1] + r2 * (I.p[3] - I.p[1])), meta_plane(I.meta));
         dl = pt - lo;
     } else {
-        // sphere::random (primitive.h:51-58) + random_to_sphere (random.h:46-55)
-        V3 center = v3(I.p[0], I.p[1], I.p[2]);
-        float radius = I.p[3];
-        V3 direction = center - lo;
-        float distance_squared = squared_length(direction);
-        Onb uvw = onb_from_w(direction);
-        float z = 1 + r2 * (sqrtf(1 - radius * radius / distance_squared) - 1);
-        float phi = 2 * PT_PI_F * r1;
-        float sq = sqrtf(1 - z * z);
-        dl = onb_local(uvw, v3(cosf(phi) * sq, sinf(phi) * sq, z));
+        dl = sphere_random(v3(I.p[0], I.p[1], I.p[2]), I.p[3], lo, r1, r2);
     }
     return xform_vector(fwd, dl);
 }
