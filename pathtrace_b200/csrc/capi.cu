@@ -639,8 +639,9 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
             throw std::runtime_error("config: unsupported integrator");
         if (c.max_bounces < 0 || c.max_bounces > 4096)
             throw std::runtime_error("config: max_bounces out of range");
-        if (c.integrator == B200PT_INTEGRATOR_INEEPT && (c.light_samples < 0 || c.light_samples > 1024))
-            throw std::runtime_error("config: light_samples out of range");
+        // integrator.h:265 divides the light sum by light_samples: with 0 every sample that reaches a surface is NaN
+        if (c.integrator == B200PT_INTEGRATOR_INEEPT && (c.light_samples < 1 || c.light_samples > 1024))
+            throw std::runtime_error("config: light_samples must be in [1, 1024] for \"iterative nee path tracing\"");
         if (c.device != scene->device)
             throw std::runtime_error("config.device differs from the device the scene was uploaded to");
         need_device(scene);

@@ -200,3 +200,68 @@ def test_render_matches_reference_golden(tag):
     assert (np.abs(z) > 6).mean() < 1e-3, np.abs(z).max()
     # deterministic pixels (zero variance on both sides) must agree outright
     np.testing.assert_allclose(mean_g[~ok], mean_r[~ok], rtol=1e-4, atol=1e-6)
+
+
+def _many_lights_scene(n_lights, n_spheres):
+    """A floor, `n_lights` small rect/sphere lights above it and `n_spheres` diffuse / glass / metal spheres: with more
+    than 8 emitters NEE falls back to the plain closest-hit shadow query, with more than 16 instances to the BVH."""
+    rng = np.random.Generator(np.random.PCG64(11))
+    mats = [{"id": "white", "type": "lambertian", "data": {"color": [0.7, 0.7, 0.7]}},
+            {"id": "blue", "type": "lambertian", "data": {"color": [0.2, 0.3, 0.8]}},
+            {"id": "glass", "type": "dielectric", "data": {"ior": 1.5}},
+            {"id": "steel", "type": "metal", "data": {"color": [0.8, 0.8, 0.9]}},
+            {"id": "light", "type": "diffuse_light", "data": {"color": [12.0, 11.0, 9.0]}}]
+    inst = [{"type": "direct", "primitive": {"type": "rect", "material": {"id": "white"}, "size": [60, 60]}}]
+    for k in range(n_lights):
+        x, z = (k % 4) * 10.0 - 15.0, (k // 4) * 10.0 - 10.0
+        prim = ({"type": "rect", "material": {"id": "light"}, "size": [3, 3]} if k % 2 == 0 else
+                {"type": "sphere", "material": {"id": "light"}, "radius": 1.0})
+        inst.append({"type": "direct", "primitive": prim, "transform": {"translate": [x, 12.0 + (k % 3), z]}})
+    for k in range(n_spheres):
+        p = rng.uniform([-20, 1.5, -15], [20, 1.5, 15])
+        inst.append({"type": "direct", "primitive": {"type": "sphere", "material": {"id": ["blue", "glass", "steel"][k % 3]},
+                                                     "radius": 1.5},
+                     "transform": {"translate": [float(p[0]), float(p[1]), float(p[2])]}})
+    return {"camera": {"look_from": [0.0, 18.0, -45.0], "look_at": [0.0, 3.0, 0.0], "fov": 40.0, "aperture": 0.0,
+                       "dist_to_focus": 40.0},
+            "world": {"color": [0.02, 0.02, 0.03]}, "assets": [], "textures": [], "materials": mats, "primitives": [],
+            "instances": inst}
+
+
+@pytest.mark.parametrize("n_lights,n_spheres,over", [(12, 3, dict()), (12, 20, dict()), (3, 20, dict(light_samples=2)),
+                                                     (9, 0, dict(light_samples=5, max_bounces=3))])
+def test_many_lights_and_mid_size_scenes(tmp_path, n_lights, n_spheres, over):
+    """The kernel variants the shipped scenes do not reach: > 8 emitters (closest-hit shadow query, `ANY` = false) on
+    the small-scene table and on the BVH, and a BVH scene with few emitters; sphere AND rect lights; light_samples
+    that are not a power of two (atomics instead of the butterfly).  GPU against the CPU restatement."""
+    path = str(tmp_path / "many_lights.json")
+    with open(path, "w") as f:
+        json.dump(_many_lights_scene(n_lights, n_spheres), f)
+    import pathtrace_b200 as pt
+    w, h, spp = 48, 32, 6
+    cfgd = pt.default_config_dict(width=w, height=h, samples=spp, scene=path, **over)
+    r, rep = _render(cfgd, batch_samples=4)
+    ref = PortOracle.from_file(path, w, h).render(make_cconfig(cfgd), stats=False)
+    _close(r.framebuffer, ref["sums"], f"{n_lights} lights, {n_spheres} spheres")
+    for k in ("rays_extension", "rays_shadow", "rays_reference"):
+        assert abs(rep[k] - ref[k]) <= 2e-3 * ref[k] + 8, (k, rep[k], ref[k])
+    assert r.framebuffer.max() > 0
+
+
+def test_degenerate_films_and_settings():
+    """1 x 1 and odd-sized films, one sample, light_samples = 1, max_bounces = 1, a sample offset beyond 2^31;
+    light_samples = 0 is refused (the reference divides by it, integrator.h:265)."""
+    import pathtrace_b200 as pt
+    with pytest.raises(Exception, match="light_samples"):
+        _render(_cfg("cornell_box", 3, 5, 2, light_samples=0))
+    for (w, h, spp, over) in [(1, 1, 1, dict()), (3, 5, 2, dict(light_samples=2)), (7, 2, 3, dict(light_samples=1, max_bounces=1)),
+                              (5, 3, 2, dict(russian_roulette=False, max_bounces=2))]:
+        cfgd = _cfg("cornell_box", w, h, spp, **over)
+        r, rep = _render(cfgd)
+        ref = PortOracle.from_file(scene_path("cornell_box"), w, h).render(make_cconfig(cfgd), stats=False)
+        assert rep["camera_rays"] == w * h * spp
+        _close(r.framebuffer, ref["sums"], (w, h, spp, over))
+    cfgd = _cfg("cornell_box", 8, 8, 2)
+    far = _render(cfgd, sample_offset=(1 << 33) + 5)[0].framebuffer
+    near = _render(cfgd, sample_offset=5)[0].framebuffer
+    assert np.isfinite(far).all() and far.max() > 0 and far.shape == near.shape
