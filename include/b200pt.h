@@ -152,6 +152,11 @@ typedef struct b200pt_config {
     float trace_probability; /* config.h:122-131: should_trace_paths ? avg_number_of_paths / (samples * pixels) : 0.
                                 Each camera sample is recorded with this probability (renderer.h:652-668) */
     int32_t trace_max_paths; /* capacity of the device-side path store; 0 = max(1024, 4 x the expected number) */
+    int32_t physically_corrected; /* config.json "physically_corrected" (default false).  0 = the reference's estimator
+                               as it is at HEAD, quirks included -- the only mode compared with the reference.  1 = a
+                               standard path tracer over the same scene (device/pt_corrected.h): specular metal with
+                               fuzz, refracting glass, emission counted once, outgoing-cosine throughput, 1/n light
+                               pick.  metal.fuzz travels in b200pt_material.power. */
 } b200pt_config;
 
 typedef struct b200pt_scene b200pt_scene;

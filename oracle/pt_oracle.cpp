@@ -17,7 +17,7 @@
 // PARITY PIN: hit routine -- exact comparison with the reference on fixed ray batches; render -- statistical
 // (clamped per-pixel z-scores) against the reference's integrator->color; no upstream golden vectors exist.
 #include "../include/b200pt.h"
-#include "../pathtrace_b200/csrc/device/pt_shade.h"
+#include "../pathtrace_b200/csrc/device/pt_corrected.h"
 #include "../pathtrace_b200/csrc/host/flat_scene.h"
 #include "../pathtrace_b200/csrc/host/scene_pack.h"
 
@@ -54,6 +54,7 @@ RenderParams make_params(const b200pt_config &c)
     rp.light_samples = c.integrator == B200PT_INTEGRATOR_INEEPT ? c.light_samples : 0;
     rp.russian_roulette = c.russian_roulette;
     rp.only_direct = c.only_direct_illumination;
+    rp.corrected = c.physically_corrected ? 1 : 0;
     rp.normal_offset = c.normal_offset;
     rp.seed_lo = (uint32_t)(c.seed & 0xffffffffull);
     rp.seed_hi = (uint32_t)(c.seed >> 32);
@@ -99,7 +100,9 @@ V3 sample_color(const PtSceneView &s, const RenderParams &rp, uint32_t pixel, ui
         PathVertexIn vin = in;
         if (s.mats[meta_material(s.inst[rec.inst].meta)].kind != B200PT_MAT_DIFFUSE_LIGHT)
             vin.attenuation = v3(0.f, 0.f, 0.f);
-        if (nee)
+        if (rp.corrected)
+            shade_hit_corrected(s, rp, vin, rec, rnd, out);
+        else if (nee)
             shade_hit_ineept(s, rp, vin, rec, rnd, out);
         else
             shade_hit_rpt(s, rp, vin, rec, b, rnd, out);
@@ -109,7 +112,8 @@ V3 sample_color(const PtSceneView &s, const RenderParams &rp, uint32_t pixel, ui
         if (out.want_nee) {
             V3 light = v3(0.f, 0.f, 0.f);
             for (int k = 0; k < rp.light_samples; k++) {
-                light += nee_sample<false>(s, rp, key, b, k, rec.p, rec.n, out.mat_kind, out.W, nullptr);
+                light += rp.corrected ? nee_sample_corrected<false>(s, key, b, k, rec.p, rec.n, out.mat_kind, out.W, nullptr)
+                                      : nee_sample<false>(s, rp, key, b, k, rec.p, rec.n, out.mat_kind, out.W, nullptr);
                 cnt.shadow++;
             }
             sum += light / (float)rp.light_samples;

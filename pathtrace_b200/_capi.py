@@ -63,7 +63,8 @@ class Config(C.Structure):
                 ("block_width", C.c_int32), ("block_height", C.c_int32), ("threads", C.c_int32),
                 ("seed", C.c_uint64), ("sample_offset", C.c_int64), ("device", C.c_int32),
                 ("batch_samples", C.c_int32), ("stats_clamp", C.c_float), ("profile", C.c_int32),
-                ("trace_probability", C.c_float), ("trace_max_paths", C.c_int32)]
+                ("trace_probability", C.c_float), ("trace_max_paths", C.c_int32),
+                ("physically_corrected", C.c_int32)]
 
 
 class Progress(C.Structure):

@@ -673,6 +673,9 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         rp.light_samples = c.integrator == B200PT_INTEGRATOR_INEEPT ? c.light_samples : 0;
         rp.russian_roulette = c.russian_roulette;
         rp.only_direct = c.only_direct_illumination;
+        rp.corrected = c.physically_corrected ? 1 : 0;
+        if (rp.corrected && c.profile == 2)
+            throw std::runtime_error("config: profile = 2 (work counters) is not built for the physically_corrected mode");
         rp.normal_offset = c.normal_offset;
         rp.seed_lo = (uint32_t)(c.seed & 0xffffffffull);
         rp.seed_hi = (uint32_t)(c.seed >> 32);

@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(kExtThreads) k_extend(PtSceneView s, RenderPar
 }
 
 // One instantiation per (shade queue, integrator): each holds the code of its own materials only.
-template <int kind, bool NEE>
+template <int kind, bool NEE, bool CORR>
 __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
     const long long sample_base = wf.ctl->sample_base;
@@ -273,7 +273,9 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
                 RngKey key = make_key(rp, wf, slot, sample_base);
                 F4 rnd = rng4(key, stage_word(bounce, RNG_SHADE, 0), 0);
                 PathVertexOut out;
-                if (NEE)
+                if (CORR)
+                    shade_hit_corrected<kind>(s, rp, in, rec, rnd, out);
+                else if (NEE)
                     shade_hit_ineept<kind>(s, rp, in, rec, rnd, out);
                 else
                     shade_hit_rpt<kind>(s, rp, in, rec, bounce, rnd, out);
@@ -310,7 +312,8 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
 #define PT_NEE_MEDIA_MINB 4
 #endif
 // ANY: the scene has at most PT_MAX_DIRECT_EMITTERS emitters -> emitters first, then an any-hit walk (trace_shadow)
-template <bool COUNT, bool MEDIA, bool ANY, bool SMALL>
+// CORR: the estimator of pt_corrected.h instead of the reference's
+template <bool COUNT, bool MEDIA, bool ANY, bool SMALL, bool CORR>
 __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
     static_assert(ANY || !SMALL, "the small-scene walk is instantiated for the any-hit shadow query only");
@@ -350,7 +353,10 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
             float4 hp = wf.hit_p[slot], hn = wf.hit_n[slot], w = wf.nee_w[slot];
             RngKey key = make_key(rp, wf, slot, sample_base);
             nrays++;
-            nee_prepare(s, key, bounce, k, xyz(hp), xyz(hn), __float_as_int(w.w), xyz(w), ns);
+            if (CORR)
+                nee_prepare_corrected(s, key, bounce, k, xyz(hp), xyz(hn), __float_as_int(w.w), xyz(w), ns);
+            else
+                nee_prepare(s, key, bounce, k, xyz(hp), xyz(hn), __float_as_int(w.w), xyz(w), ns);
             mr = nee_medium_rng(key, bounce, k);
             T.init(xyz(hp), ns.dir, 0.001f, PT_FLT_MAX);
             trace = !nee_is_void(ns);
@@ -370,7 +376,7 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
         if (trace && (!ANY || T.best_inst == lit)) {
             Hit lrec;
             const bool hit = T.template result<MEDIA>(s, lrec, !ANY || s.emit_needs_p != 0);
-            c = nee_finish(s, ns, hit, lrec);
+            c = CORR ? nee_finish_corrected(s, ns, hit, lrec) : nee_finish(s, ns, hit, lrec);
         }
         if (pow2) {
             // lanes [g*L, (g+1)*L) hold one vertex (kThreads and 32 are multiples of L): fixed-order butterfly over
@@ -668,10 +674,12 @@ void launch_shade(const PtSceneView &s, const RenderParams &rp, const Wavefront 
     const bool nee = rp.integrator == B200PT_INTEGRATOR_INEEPT;
 #define PT_LAUNCH_SHADE(K)                                                  \
     case K:                                                                 \
-        if (nee)                                                            \
-            k_shade<K, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);  \
-        else                                                                \
-            k_shade<K, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce); \
+        if (rp.corrected)                                                          \
+            k_shade<K, false, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);  \
+        else if (nee)                                                              \
+            k_shade<K, true, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);  \
+        else                                                                       \
+            k_shade<K, false, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce); \
         break;
     switch (kind) {
         PT_LAUNCH_SHADE(SK_MISS)
@@ -688,21 +696,25 @@ void launch_nee(const PtSceneView &s, const RenderParams &rp, const Wavefront &w
 {
     const bool any = s.n_emitters <= PT_MAX_DIRECT_EMITTERS;
     const bool small = any && s.n_small > 0;
-#define PT_LAUNCH_NEE(C, M)                                                            \
+#define PT_LAUNCH_NEE(C, M, X)                                                          \
     do {                                                                               \
-        if (small)                                                                     \
-            k_nee<C, M, true, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);   \
-        else if (any)                                                                  \
-            k_nee<C, M, true, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);  \
-        else                                                                           \
-            k_nee<C, M, false, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce); \
+        if (small)                                                                            \
+            k_nee<C, M, true, true, X><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);   \
+        else if (any)                                                                         \
+            k_nee<C, M, true, false, X><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);  \
+        else                                                                                  \
+            k_nee<C, M, false, false, X><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce); \
     } while (0)
-    if (lc.count_work)
-        PT_LAUNCH_NEE(true, true);
+    if (rp.corrected && s.n_media > 0)
+        PT_LAUNCH_NEE(false, true, true);
+    else if (rp.corrected)
+        PT_LAUNCH_NEE(false, false, true);
+    else if (lc.count_work)
+        PT_LAUNCH_NEE(true, true, false);
     else if (s.n_media > 0)
-        PT_LAUNCH_NEE(false, true);
+        PT_LAUNCH_NEE(false, true, false);
     else
-        PT_LAUNCH_NEE(false, false);
+        PT_LAUNCH_NEE(false, false, false);
 #undef PT_LAUNCH_NEE
 }
 

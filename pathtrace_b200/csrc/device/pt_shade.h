@@ -12,6 +12,7 @@ struct RenderParams {
     int32_t integrator; // B200PT_INTEGRATOR_*
     int32_t max_bounces, light_samples;
     int32_t russian_roulette, only_direct;
+    int32_t corrected; // config.physically_corrected (pt_corrected.h)
     float normal_offset;
     uint32_t seed_lo, seed_hi;
 };

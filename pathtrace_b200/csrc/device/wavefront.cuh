@@ -8,7 +8,7 @@
 //
 // Queue sizes live in `counters` on the device (row = bounce), so the host never waits between kernels.
 #pragma once
-#include "pt_shade.h"
+#include "pt_corrected.h"
 
 #include <cuda_runtime.h>
 

@@ -64,6 +64,7 @@ ParsedConfig parse_config(const Json &j)
     if (out.should_trace_paths)
         c.trace_probability = (float)(j.value("avg_number_of_paths", 100.0) / (double)((long)c.samples * ((long)c.width * c.height)));
     c.trace_max_paths = (int32_t)j.value("trace_max_paths", 0);
+    c.physically_corrected = j.value("physically_corrected", false) ? 1 : 0;
 
     if (c.width <= 0 || c.height <= 0)
         throw std::runtime_error("config: film size must be positive");

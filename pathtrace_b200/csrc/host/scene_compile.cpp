@@ -220,8 +220,11 @@ void parse_materials(Builder &b, const Json &scene)
                 json_vec3(data["color"], c);
             else
                 c[0] = c[1] = c[2] = 1.f;
-            // fuzz (material.h:79-89) is stored and never read; it is not carried over.
-            b.materials.emplace(id, std::make_pair(b.add_material(B200PT_MAT_METAL, -1, c), std::string("metal")));
+            // fuzz (material.h:79-89) is stored and never read by the reference; it travels in `power` for the opt-in
+            // corrected mode (device/pt_corrected.h)
+            float fuzz = (float)data.value("roughness", 0.0);
+            fuzz = fuzz < 1.f ? fuzz : 1.f;
+            b.materials.emplace(id, std::make_pair(b.add_material(B200PT_MAT_METAL, -1, c, 1.45f, fuzz), std::string("metal")));
         } else if (type == "dielectric") {
             float ri = 1.450f;
             if (data.contains("ior"))

@@ -75,7 +75,8 @@ class _CConfig(C.Structure):  # mirrors b200pt_config (include/b200pt.h)
                 ("block_width", C.c_int32), ("block_height", C.c_int32), ("threads", C.c_int32),
                 ("seed", C.c_uint64), ("sample_offset", C.c_int64), ("device", C.c_int32),
                 ("batch_samples", C.c_int32), ("stats_clamp", C.c_float), ("profile", C.c_int32),
-                ("trace_probability", C.c_float), ("trace_max_paths", C.c_int32)]
+                ("trace_probability", C.c_float), ("trace_max_paths", C.c_int32),
+                ("physically_corrected", C.c_int32)]
 
 
 INTEGRATORS = {"iterative nee path tracing": 4, "recursive path tracing": 0}
@@ -97,6 +98,7 @@ def make_cconfig(config_dict, **over):
     c.only_direct_illumination = int(bool(config_dict.get("only_direct_illumination", False)))
     c.normal_offset = float(config_dict.get("normal_offset", 0.0001))
     c.seed = int(config_dict.get("seed", 0))
+    c.physically_corrected = int(bool(config_dict.get("physically_corrected", False)))
     for k, v in over.items():
         setattr(c, k, v)
     return c

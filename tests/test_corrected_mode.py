@@ -1,0 +1,108 @@
+"""The opt-in "physically corrected" estimator (config "physically_corrected": true; device/pt_corrected.h, SURVEY.md 8f
+rank 4).  It has no counterpart in the reference -- it is what the reference's quirks (Q2-Q7) deviate from -- so it is
+checked (a) GPU against the CPU restatement, sample for sample, like every other mode, and (b) as an ESTIMATOR: next
+event estimation with MIS and plain path tracing are two unbiased estimators of the same integral and must agree
+per pixel within their standard errors; the reference's own pair (NEEIterative / RecursivePT) does not."""
+import numpy as np
+import pytest
+
+from conftest import scene_path
+from oracle_lib import PortOracle, make_cconfig
+
+W, H = 20, 16
+
+
+def _cfgd(scene, spp, **over):
+    import pathtrace_b200 as pt
+    return pt.default_config_dict(width=W, height=H, samples=spp, scene=scene_path(scene), physically_corrected=True,
+                                  max_bounces=12, **over)
+
+
+def _z(a, b, n):
+    """per-pixel z-scores of two clamped-sample statistics dicts (sum, sum of squares over n samples each)"""
+    ma, mb = a["csum"].astype(np.float64) / n, b["csum"].astype(np.float64) / n
+    va = np.maximum(a["csq"].astype(np.float64) / n - ma ** 2, 0) / (n - 1)
+    vb = np.maximum(b["csq"].astype(np.float64) / n - mb ** 2, 0) / (n - 1)
+    se = np.sqrt(va + vb)
+    ok = se > 0
+    return (ma[ok] - mb[ok]) / se[ok], ma, mb
+
+
+@pytest.mark.parametrize("scene", ["cornell_box", "three_orbs"])
+def test_nee_with_mis_agrees_with_plain_path_tracing_cpu(scene):
+    n = 768
+    stats = {}
+    for integ in ("iterative nee path tracing", "recursive path tracing"):
+        cfgd = _cfgd(scene, n, integrator_type=integ, light_samples=1)
+        c = make_cconfig(cfgd, stats_clamp=1.0e9)
+        assert c.physically_corrected == 1
+        stats[integ] = PortOracle.from_file(scene_path(scene), W, H).render(c)
+    z, ma, mb = _z(stats["iterative nee path tracing"], stats["recursive path tracing"], n)
+    assert ma.mean() > 0.01
+    if scene == "cornell_box":
+        assert abs(ma.mean() - mb.mean()) < 0.05 * mb.mean(), (ma.mean(), mb.mean())
+        assert (np.abs(z) > 4).mean() < 0.01 and abs(z.mean()) < 0.25, ((np.abs(z) > 4).mean(), z.mean())
+    else:
+        # a 5 x 5 light seen by plain path tracing: a few hundred hits of radiance 25 in the whole image -- per-pixel
+        # variances are not estimable (most pixels have no hit at all), the image mean is (about 4 % standard error)
+        assert abs(ma.mean() - mb.mean()) < 0.15 * mb.mean(), (ma.mean(), mb.mean())
+    # ... and the reference's estimators are a different thing: twice the emission, n^2 light weights, cos_i / cos_s
+    plain = PortOracle.from_file(scene_path(scene), W, H).render(
+        make_cconfig(dict(_cfgd(scene, 64), physically_corrected=False), stats_clamp=1.0e9))
+    assert abs(plain["csum"].mean() / 64 - mb.mean()) > 0.05 * mb.mean()
+
+
+def test_config_key_and_metal_fuzz():
+    import pathtrace_b200 as pt
+    cfg = pt.Config.from_json(_cfgd("light_test", 4))
+    assert cfg.physically_corrected == 1
+    assert pt.Config.from_json(pt.default_config_dict()).physically_corrected == 0
+    flat = pt.Scene.from_file(scene_path("light_test"), 8, 8, device=-1).describe()
+    fuzz = sorted(round(m["power"], 3) for m in flat["materials"] if m["kind"] == 1)
+    assert fuzz == [0.1, 0.2, 0.3]  # "roughness" of metal1..3 (scenes/light_test.json), carried in `power`
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("scene,over", [("three_orbs", dict()), ("cornell_box", dict()), ("cornell_box_with_volume", dict()),
+                                        ("light_test", dict(light_samples=2)), ("book2_final", dict(max_bounces=4)),
+                                        ("cornell_box", dict(integrator_type="recursive path tracing")),
+                                        ("cornell_box_image_textures", dict())])
+def test_gpu_matches_cpu_restatement(scene, over):
+    import pathtrace_b200 as pt
+    w, h, spp = 48, 40, 6
+    cfgd = pt.default_config_dict(width=w, height=h, samples=spp, scene=scene_path(scene), physically_corrected=True, **over)
+    cfg = pt.Config.from_json(cfgd).replace(batch_samples=4)
+    sc = pt.Scene.from_file(cfg.scene_path, w, h, device=0)
+    r = pt.renderer_from_config(sc, cfg).start_render()
+    rep = r.finalize()
+    ref = PortOracle.from_file(scene_path(scene), w, h).render(make_cconfig(cfgd), stats=False)
+    a, b = r.framebuffer, ref["sums"]
+    scale = np.maximum(np.abs(b), 1e-3 * max(1.0, float(np.abs(b).max())))
+    assert float((np.abs(a - b) / scale > 1e-3).mean()) < 1e-2
+    assert abs(float(a.sum()) - float(b.sum())) <= 1e-2 * abs(float(b.sum())) + 1e-6
+    for k in ("rays_extension", "rays_shadow"):
+        assert abs(rep[k] - ref[k]) <= 2e-3 * ref[k] + 8, (k, rep[k], ref[k])
+
+
+@pytest.mark.gpu
+def test_gpu_nee_agrees_with_plain_path_tracing_at_depth():
+    """The same estimator check on the GPU with enough samples to see 1 % effects: cornell_box, 4096 spp."""
+    import pathtrace_b200 as pt
+    n, w, h = 4096, 48, 48
+    out = {}
+    for integ in ("iterative nee path tracing", "recursive path tracing"):
+        cfgd = pt.default_config_dict(width=w, height=h, samples=n, scene=scene_path("cornell_box"),
+                                      physically_corrected=True, max_bounces=16, integrator_type=integ)
+        cfg = pt.Config.from_json(cfgd).replace(stats_clamp=1.0e9)
+        sc = pt.Scene.from_file(cfg.scene_path, w, h, device=0)
+        r = pt.renderer_from_config(sc, cfg).start_render()
+        r.finalize()
+        s, q = r.stats()
+        out[integ] = {"csum": s, "csq": q}
+    z, ma, mb = _z(out["iterative nee path tracing"], out["recursive path tracing"], n)
+    assert abs(ma.mean() - mb.mean()) < 0.02 * mb.mean(), (ma.mean(), mb.mean())
+    assert (np.abs(z) > 4).mean() < 0.005 and abs(z.mean()) < 0.15, ((np.abs(z) > 4).mean(), z.mean())
+    # finite variance: NEE + MIS is far less noisy than plain path tracing on a small light
+    va = (out["iterative nee path tracing"]["csq"].astype(np.float64) / n - ma ** 2).mean()
+    vb = (out["recursive path tracing"]["csq"].astype(np.float64) / n - mb ** 2).mean()
+    assert va < 0.5 * vb
