@@ -164,7 +164,8 @@ static int trace_impl(void *scene, const float *rays, size_t n, const float *med
 {
     OracleScene *sc = (OracleScene *)scene;
     PtSceneView view = sc->view;
-    view.emit_needs_p = 1; // report p of shadow hits too (renders skip it when every emitter has a constant texture)
+    view.emit_needs_n = 1;
+    view.emit_needs_p = 1; // report p and n of shadow hits too (renders skip it when every emitter has a constant texture)
     for (size_t i = 0; i < n; i++) {
         const float *q = rays + i * 8;
         MediumRng mr;

@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
         }
         if (trace && (!ANY || T.best_inst == lit)) {
             Hit lrec;
-            const bool hit = T.template result<MEDIA>(s, lrec, !ANY || s.emit_needs_p != 0);
+            const bool hit = T.template result<MEDIA>(s, lrec, !ANY || s.emit_needs_p != 0, !ANY || s.emit_needs_n != 0);
             c = CORR ? nee_finish_corrected(s, ns, hit, lrec) : nee_finish(s, ns, hit, lrec);
         }
         if (pow2) {

@@ -679,12 +679,22 @@ struct Traversal {
 #endif
 
     // instance::hit epilogue (primitive.h:302-305): p and normal back to world space, rec.u / rec.v
-    // want_p = false (shadow hits on emitters with constant textures): only instance, t and normal are filled in
-    template <bool MEDIA> PT_HD bool result(const PtSceneView &s, Hit &out, bool want_p = true) const
+    // want_p = false (shadow hits on emitters with constant textures): only instance, t and normal are filled in;
+    // want_n = false (... that are all two-sided): not even the normal -- emission does not look at it
+    template <bool MEDIA> PT_HD bool result(const PtSceneView &s, Hit &out, bool want_p = true, bool want_n = true) const
     {
         if (best_inst < 0) {
             out.inst = -1;
             return false;
+        }
+        if (!want_p && !want_n) {
+            out.inst = best_inst;
+            out.t = best.t;
+            out.p = v3(0.f, 0.f, 0.f);
+            out.n = v3(0.f, 0.f, 0.f);
+            out.u = out.v = 0.f;
+            out.face = best.face;
+            return true;
         }
         InstanceData I;
         load_instance(s.inst, best_inst, I);
@@ -748,7 +758,7 @@ PT_HD bool trace_shadow(const PtSceneView &s, V3 o, V3 d, float t_min, float t_m
         T.template run<COUNT, MEDIA, true>(s, mr, counters);
     if (T.best_inst != lit)
         return false;
-    return T.template result<MEDIA>(s, out, s.emit_needs_p != 0);
+    return T.template result<MEDIA>(s, out, s.emit_needs_p != 0, s.emit_needs_n != 0);
 }
 
 } // namespace pt

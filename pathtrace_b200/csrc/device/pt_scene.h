@@ -88,6 +88,7 @@ struct PtSceneView {
     const float *perlin_ranvec; // 256 x 3
     const int32_t *perlin_perm; // 3 x 256
     int32_t n_nodes, n_inst, n_lights, n_emitters, n_small, n_images, background;
+    int32_t emit_needs_n; // some emitter is one-sided: shadow hits must report the normal (material.h:215-222)
     int32_t emit_needs_p; // some emitter has a non-constant texture: shadow hits must report p (else only the normal)
     int32_t n_media; // instances wrapped in a constant_medium; 0 selects the kernels compiled without that branch
     PtCamera cam;

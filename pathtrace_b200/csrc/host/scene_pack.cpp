@@ -116,6 +116,10 @@ pt::PtSceneView PackedScene::host_view(const FlatScene &f) const
     v.background = f.background;
     v.n_media = n_media;
     v.emit_needs_p = 0;
+    v.emit_needs_n = 0;
+    for (const b200pt_material &m : f.materials)
+        if (m.kind == B200PT_MAT_DIFFUSE_LIGHT && !m.two_sided)
+            v.emit_needs_n = 1;
     for (const b200pt_material &m : f.materials)
         if (m.kind == B200PT_MAT_DIFFUSE_LIGHT &&
             !(m.texture >= 0 && m.texture < (int)f.textures.size() && f.textures[m.texture].kind == B200PT_TEX_CONSTANT))
