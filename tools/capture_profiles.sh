@@ -17,7 +17,7 @@ ncu --set full --clock-control none --import-source on -k regex:k_nee -s 21 -c 3
     $BENCH > $OUT/ncu_nee.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:k_extend -s 21 -c 3 -f -o $OUT/${TAG}_extend_cornell_box \
     $BENCH > $OUT/ncu_ext.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:k_shade -s 106 -c 1 -f -o $OUT/${TAG}_shade_cornell_box \
+ncu --set full --clock-control none --import-source on -k regex:k_shade -s 181 -c 1 -f -o $OUT/${TAG}_shade_cornell_box \
     $BENCH > $OUT/ncu_shade.log 2>&1
 B2="python bench.py --scene book2_final --steps 1 --warmup 3 --no-cpu-baseline"
 ncu --set full --clock-control none --import-source on -k regex:k_extend -s 11 -c 2 -f -o $OUT/${TAG}_extend_book2_final \
