@@ -189,7 +189,7 @@ int b200pt_scene_create_from_file(const char *scene_path, int32_t film_width, in
 int b200pt_scene_create(const b200pt_scene_desc *desc, int32_t device, b200pt_scene **out);
 /* Borrow the compiled flat description (valid until the scene is destroyed). */
 int b200pt_scene_get_desc(const b200pt_scene *scene, b200pt_scene_desc *out);
-/* BVH statistics: n_nodes, depth, and the scene bounds. */
+/* Statistics of the tree the kernels walk (4 children per node): n_nodes, depth, and the scene bounds. */
 int b200pt_scene_bvh_info(const b200pt_scene *scene, int32_t *n_nodes, int32_t *max_depth, float bounds[6]);
 void b200pt_scene_destroy(b200pt_scene *scene);
 

@@ -279,7 +279,7 @@ void upload_scene(b200pt_scene &sc)
     CK(cudaStreamCreateWithFlags(&sc.stream, cudaStreamNonBlocking));
     auto up = [&](const auto &vec) { return dev_upload(vec, sc.device, sc.allocations); };
     pt::PtSceneView &v = sc.view;
-    v.nodes = (up(sc.packed.bvh.nodes));
+    v.nodes = (up(sc.packed.bvh.nodes4));
     v.inst = (up(sc.packed.inst));
     v.fwd = (up(sc.packed.fwd));
     v.mats = (up(sc.flat.materials));
@@ -520,9 +520,9 @@ int b200pt_scene_bvh_info(const b200pt_scene *scene, int32_t *n_nodes, int32_t *
     if (!scene)
         return fail(B200PT_ERR_INVALID, "null argument");
     if (n_nodes)
-        *n_nodes = (int32_t)scene->packed.bvh.nodes.size();
+        *n_nodes = (int32_t)scene->packed.bvh.nodes4.size();
     if (max_depth)
-        *max_depth = scene->packed.bvh.max_depth;
+        *max_depth = scene->packed.bvh.max_depth4;
     if (bounds)
         memcpy(bounds, scene->packed.bvh.bounds, sizeof(float) * 6);
     return B200PT_OK;

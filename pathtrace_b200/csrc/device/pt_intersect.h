@@ -411,7 +411,6 @@ struct TraceCounters {
     uint32_t boxes, prims;
 };
 
-#define PT_STACK_DEPTH 48
 #define PT_MAX_DIRECT_EMITTERS 8 // more emitters than this: shadow rays fall back to the plain closest-hit query
 
 // World::hit (world.h:17-20) as a resumable state machine: init() -> steps until one returns false -> result().
@@ -455,64 +454,86 @@ struct Traversal {
         return false;
     }
 
-    // One inner node (cur >= 0): slab tests of both children, descend into the nearer one, push the other.
-    // Returns false when the traversal is complete.
-    template <bool COUNT> PT_HD bool node_step(const PtSceneView &s, TraceCounters *counters)
+    // One inner node (cur >= 0) of the 4-wide tree: slab tests of its (up to) four children, descend into the nearest
+    // one that is hit, push the others farthest first.  Returns false when the traversal is complete.
+    template <bool COUNT, bool SORT = true> PT_HD bool node_step(const PtSceneView &s, TraceCounters *counters)
     {
-        const PtNode *node = s.nodes + cur;
+        const PtNode4 *node = s.nodes + cur;
+        float e[4];
+        int32_t ref[4];
 #if defined(__CUDA_ARCH__)
         const float4 *q = reinterpret_cast<const float4 *>(node);
-        float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), e = __ldg(q + 3);
-        float lo0[3] = {a.x, a.y, a.z}, hi0[3] = {b.x, b.y, b.z}, lo1[3] = {c.x, c.y, c.z}, hi1[3] = {e.x, e.y, e.z};
-        int32_t ref0 = __float_as_int(a.w), ref1 = __float_as_int(c.w);
+        const float4 lx = __ldg(q), ly = __ldg(q + 1), lz = __ldg(q + 2), hx = __ldg(q + 3), hy = __ldg(q + 4),
+                     hz = __ldg(q + 5);
+        const int4 r = __ldg(reinterpret_cast<const int4 *>(q + 6));
+        const float lox[4] = {lx.x, lx.y, lx.z, lx.w}, loy[4] = {ly.x, ly.y, ly.z, ly.w}, loz[4] = {lz.x, lz.y, lz.z, lz.w};
+        const float hix[4] = {hx.x, hx.y, hx.z, hx.w}, hiy[4] = {hy.x, hy.y, hy.z, hy.w}, hiz[4] = {hz.x, hz.y, hz.z, hz.w};
+        ref[0] = r.x, ref[1] = r.y, ref[2] = r.z, ref[3] = r.w;
 #else
-        const float *lo0 = node->lo0, *hi0 = node->hi0, *lo1 = node->lo1, *hi1 = node->hi1;
-        int32_t ref0 = node->ref0, ref1 = node->ref1;
+        const float *lox = node->lox, *loy = node->loy, *loz = node->loz, *hix = node->hix, *hiy = node->hiy,
+                    *hiz = node->hiz;
+        for (int k = 0; k < 4; k++)
+            ref[k] = node->ref[k];
 #endif
-        float e0, e1;
         const float lim = cull_limit(best_t);
-        bool h0 = hit_aabb(lo0, hi0, o, inv_d, t_min, lim, e0);
-        bool h1 = hit_aabb(lo1, hi1, o, inv_d, t_min, lim, e1);
-        if (COUNT)
-            counters->boxes += 2;
-        if (h0 && h1) {
-            int32_t near_ref = ref0, far_ref = ref1;
-            float far_t = e1;
-            if (e1 < e0) {
-                near_ref = ref1;
-                far_ref = ref0;
-                far_t = e0;
-            }
-            if (sp < PT_STACK_DEPTH) {
-                stack_ref[sp] = far_ref;
-                stack_t[sp] = far_t;
+        const float never = __builtin_huge_valf();
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int k = 0; k < 4; k++) {
+            const float lo[3] = {lox[k], loy[k], loz[k]}, hi[3] = {hix[k], hiy[k], hiz[k]};
+            const bool used = ref[k] != PT_NO_CHILD;
+            if (COUNT && used)
+                counters->boxes += 1;
+            if (!(used && hit_aabb(lo, hi, o, inv_d, t_min, lim, e[k])))
+                e[k] = never;
+        }
+        // sorting network, nearest first
+#define PT_CSWAP(a, b)                                                                                                 \
+    if (e[b] < e[a]) {                                                                                                 \
+        const float te = e[a];                                                                                         \
+        e[a] = e[b], e[b] = te;                                                                                        \
+        const int32_t tr = ref[a];                                                                                     \
+        ref[a] = ref[b], ref[b] = tr;                                                                                  \
+    }
+        if (SORT) {
+            PT_CSWAP(0, 1)
+            PT_CSWAP(2, 3)
+            PT_CSWAP(0, 2)
+            PT_CSWAP(1, 3)
+            PT_CSWAP(1, 2)
+        } else {
+            // any order will do: only bring a child that was hit to the front
+            PT_CSWAP(0, 1)
+            PT_CSWAP(2, 3)
+            PT_CSWAP(0, 2)
+        }
+#undef PT_CSWAP
+        if (!(e[0] < never))
+            return pop();
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int k = 3; k >= 1; k--)
+            if (e[k] < never && sp < PT_STACK_DEPTH) {
+                stack_ref[sp] = ref[k];
+                stack_t[sp] = e[k];
                 sp++;
             }
-            cur = near_ref;
-            return true;
-        }
-        if (h0) {
-            cur = ref0;
-            return true;
-        }
-        if (h1) {
-            cur = ref1;
-            return true;
-        }
-        return pop();
+        cur = ref[0];
+        return true;
     }
 
-    // One leaf (cur < 0): the instance ~cur.  Returns false when the traversal is complete.
+    // One leaf: instance idx against [t_min, best_t].  Returns true when the traversal must end here.
     // ANY = true is the occlusion phase of a shadow query (see emitters_first): emitters were tested already and the
     // first accepted hit ends the traversal.
     template <bool COUNT, bool MEDIA, bool ANY = false>
-    PT_HD bool leaf_step(const PtSceneView &s, const MediumRng &mr, TraceCounters *counters)
+    PT_HD bool leaf_test(const PtSceneView &s, int idx, const MediumRng &mr, TraceCounters *counters)
     {
-        const int idx = ~cur;
         InstanceData I;
         load_instance(s.inst, idx, I);
         if (ANY && meta_emitter(I.meta))
-            return pop();
+            return false;
         PrimHit h;
         if (COUNT)
             counters->prims += 1;
@@ -526,8 +547,18 @@ struct Traversal {
             best = h;
             best_inst = idx;
             if (ANY)
-                return false; // occluded: nothing nearer can change the answer
+                return true; // occluded: nothing nearer can change the answer
         }
+        return false;
+    }
+
+    // One leaf step (cur < 0): the instance ~cur, then the next pending node.  Returns false when the traversal is
+    // complete.
+    template <bool COUNT, bool MEDIA, bool ANY = false>
+    PT_HD bool leaf_step(const PtSceneView &s, const MediumRng &mr, TraceCounters *counters)
+    {
+        if (leaf_test<COUNT, MEDIA, ANY>(s, ~cur, mr, counters))
+            return false;
         return pop();
     }
 
@@ -671,7 +702,7 @@ struct Traversal {
         while (__any_sync(0xffffffffu, active)) {
             while (__any_sync(0xffffffffu, active && cur >= 0))
                 if (active && cur >= 0)
-                    active = node_step<COUNT>(s, counters);
+                    active = node_step<COUNT, !ANY>(s, counters); // an occlusion query does not care for the order
             if (active) // cur < 0 here
                 active = leaf_step<COUNT, MEDIA, ANY>(s, mr, counters);
         }

@@ -1,7 +1,8 @@
 // pt_scene.h -- the device-resident scene: plain structs, 16-byte aligned, uploaded once.
 //
-//   PtNode      64 B  one BVH2 node = two 32-byte child halves {lo.xyz, ref | hi.xyz, pad}; a half is what a ray
-//                     tests (slab test) before descending, fetched as 2 x 128-bit loads.
+//   PtNode4    128 B  one node of the 4-wide BVH, child-major: {lo.x[4] | lo.y[4] | lo.z[4] | hi.x[4] | hi.y[4] | hi.z[4] |
+//                     ref[4]}, fetched as 7 x 128-bit loads; 32 bytes of it per child a ray tests (slab test).
+//   PtNode      64 B  host only: the binary SAH tree the builder makes before collapsing it.
 //   PtInstance  80 B  world->local 3x4 (48 B) + tagged-union primitive (32 B): meta word, 6 params, density.
 //   PtBox       32 B  small scenes only: the leaf box of every instance, walked linearly instead of the tree.
 //   PtFwd       48 B  local->world 3x4, fetched only for the closest hit and for light sampling.
@@ -21,6 +22,17 @@ struct alignas(16) PtNode {
     int32_t ref1;
     float hi1[3];
     int32_t pad1;
+};
+
+// The tree the kernels walk: the binary tree collapsed to 4 children per node (bvh_build.cpp collapse4), stored child-
+// major so that one 128-bit load brings the same bound of all four.  Half as many dependent node fetches per ray as
+// the binary tree, and rays of a warp agree for longer on what to do next.
+#define PT_NO_CHILD 0x7fffffff
+#define PT_STACK_DEPTH 48 // traversal stack entries per ray; scene_pack.cpp refuses a tree that could need more
+struct alignas(16) PtNode4 {
+    float lox[4], loy[4], loz[4], hix[4], hiy[4], hiz[4];
+    int32_t ref[4]; // >= 0: inner node index; < 0: ~ref = instance index; PT_NO_CHILD: empty slot
+    int32_t pad[4];
 };
 
 // meta: bits 0-1 prim kind | 2-3 rect plane | 4 rect flip | 5 medium | 6 bvh-dup | 7 light | 8-15 medium slot |
@@ -75,7 +87,7 @@ struct PtCamera {
 };
 
 struct PtSceneView {
-    const PtNode *nodes;
+    const PtNode4 *nodes;
     const PtInstance *inst;
     const PtFwd *fwd;
     const b200pt_material *mats;

@@ -1,5 +1,5 @@
 // bvh_build.cpp -- host BVH builder: binned-SAH BVH2 over instance boxes, one instance per leaf, flattened
-// depth-first into 64-byte PtNode records (two 32-byte child halves).
+// depth-first into 64-byte PtNode records (two 32-byte child halves), then collapsed into 128-byte 4-wide nodes.
 //
 // The reference builds a random-axis median-split pointer tree (bvh.h:133-175); its topology has no effect on
 // which hit is closest (every primitive is reachable through boxes that contain it), so this builder is free to
@@ -169,6 +169,80 @@ int build_range(BuildCtx &c, int begin, int end, Box &out_box, int depth)
     return me;
 }
 
+// Collapse of the binary tree: a node adopts its grandchildren in place of the inner child with the largest box,
+// until it has four children or only leaves.  Every instance stays reachable through boxes that contain it, which
+// is all the closest-hit result depends on.
+struct Child {
+    int ref;
+    float lo[3], hi[3];
+    double area() const
+    {
+        double dx = (double)hi[0] - lo[0], dy = (double)hi[1] - lo[1], dz = (double)hi[2] - lo[2];
+        return dx * dy + dy * dz + dz * dx;
+    }
+};
+
+void children_of(const pt::PtNode &n, Child out[2])
+{
+    out[0].ref = n.ref0;
+    out[1].ref = n.ref1;
+    for (int k = 0; k < 3; k++) {
+        out[0].lo[k] = n.lo0[k];
+        out[0].hi[k] = n.hi0[k];
+        out[1].lo[k] = n.lo1[k];
+        out[1].hi[k] = n.hi1[k];
+    }
+}
+
+// `stack`: the most entries a traversal below this node can have pending (its other children, then the same again
+// below the child it descends into)
+int collapse_node(const std::vector<pt::PtNode> &bin, int node, std::vector<pt::PtNode4> &out, int depth, int &max_depth,
+                  int &stack)
+{
+    max_depth = std::max(max_depth, depth + 1);
+    Child ch[4];
+    int n = 2;
+    children_of(bin[node], ch);
+    while (n < 4) {
+        int pick = -1;
+        for (int i = 0; i < n; i++)
+            if (ch[i].ref >= 0 && (pick < 0 || ch[i].area() > ch[pick].area()))
+                pick = i;
+        if (pick < 0)
+            break;
+        Child two[2];
+        children_of(bin[ch[pick].ref], two);
+        ch[pick] = two[0];
+        ch[n++] = two[1];
+    }
+    const int me = (int)out.size();
+    out.push_back(pt::PtNode4{});
+    int refs[4];
+    int below = 0;
+    for (int i = 0; i < 4; i++) {
+        refs[i] = i >= n ? PT_NO_CHILD : ch[i].ref;
+        if (i < n && ch[i].ref >= 0) {
+            int st = 0;
+            refs[i] = collapse_node(bin, ch[i].ref, out, depth + 1, max_depth, st);
+            below = std::max(below, st);
+        }
+    }
+    stack = n - 1 + below;
+    pt::PtNode4 &q = out[me];
+    for (int i = 0; i < 4; i++) {
+        const bool used = i < n;
+        q.lox[i] = used ? ch[i].lo[0] : 0.f;
+        q.loy[i] = used ? ch[i].lo[1] : 0.f;
+        q.loz[i] = used ? ch[i].lo[2] : 0.f;
+        q.hix[i] = used ? ch[i].hi[0] : 0.f;
+        q.hiy[i] = used ? ch[i].hi[1] : 0.f;
+        q.hiz[i] = used ? ch[i].hi[2] : 0.f;
+        q.ref[i] = refs[i];
+        q.pad[i] = 0;
+    }
+    return me;
+}
+
 } // namespace
 
 BuiltBvh build_bvh(const std::vector<Aabb> &boxes)
@@ -208,6 +282,8 @@ BuiltBvh build_bvh(const std::vector<Aabb> &boxes)
     }
     out.nodes = std::move(c.nodes);
     out.max_depth = c.max_depth;
+    out.nodes4.reserve(out.nodes.size() / 2 + 1);
+    collapse_node(out.nodes, 0, out.nodes4, 0, out.max_depth4, out.max_stack4);
     for (int k = 0; k < 3; k++) {
         out.bounds[k] = root.lo[k];
         out.bounds[3 + k] = root.hi[k];

@@ -68,6 +68,9 @@ PackedScene pack_scene(const FlatScene &f)
             out.texels.push_back(pt::PtTexel{im.rgba[4 * k], im.rgba[4 * k + 1], im.rgba[4 * k + 2], im.rgba[4 * k + 3]});
     }
     out.bvh = build_bvh(boxes);
+    if (out.bvh.max_stack4 > PT_STACK_DEPTH)
+        throw std::runtime_error("BVH too deep for the traversal stack (" + std::to_string(out.bvh.max_stack4) + " > " +
+                                 std::to_string(PT_STACK_DEPTH) + " pending nodes)");
     // B200PT_SMALL_MAX (tests, A/B): 0 forces the BVH path on small scenes too
     int small_max = PT_SMALL_MAX;
     if (const char *e = std::getenv("B200PT_SMALL_MAX"))
@@ -95,7 +98,7 @@ PackedScene pack_scene(const FlatScene &f)
 pt::PtSceneView PackedScene::host_view(const FlatScene &f) const
 {
     pt::PtSceneView v{};
-    v.nodes = bvh.nodes.data();
+    v.nodes = bvh.nodes4.data();
     v.inst = inst.data();
     v.fwd = fwd.data();
     v.mats = f.materials.data();
@@ -110,7 +113,7 @@ pt::PtSceneView PackedScene::host_view(const FlatScene &f) const
     v.n_emitters = (int)emitters.size();
     v.perlin_ranvec = perlin_ranvec.data();
     v.perlin_perm = perlin_perm.data();
-    v.n_nodes = (int)bvh.nodes.size();
+    v.n_nodes = (int)bvh.nodes4.size();
     v.n_inst = (int)inst.size();
     v.n_lights = (int)f.lights.size();
     v.background = f.background;

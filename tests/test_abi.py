@@ -66,7 +66,7 @@ def test_config_defaults_and_quirks():
 def test_no_cpu_fallback():
     import pathtrace_b200 as pt
     s = pt.Scene.from_file(scene_path("cornell_box"), 32, 32, device=-1)
-    assert s.bvh_info()["n_nodes"] == 7
+    assert s.bvh_info()["n_nodes"] == 4  # 8 instances: 7 binary nodes collapsed to 4-wide ones
     with pytest.raises(pt.B200ptError) as e:
         s.trace_batch(np.zeros((1, 8), np.float32))
     assert e.value.code == 3
