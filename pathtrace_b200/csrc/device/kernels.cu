@@ -241,9 +241,9 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
         if (i < n) {
             slot = q_in[i];
             float4 ro = wf.ray_o[slot], rd = wf.ray_d[slot], bt = wf.beta[slot];
-            float4 acc = wf.sum[slot];
             if (kind == SK_MISS) {
                 V3 add = shade_miss(s, xyz(rd), xyz(bt));
+                const float4 acc = wf.sum[slot];
                 wf.sum[slot] = make_float4(acc.x + add.x, acc.y + add.y, acc.z + add.z, 0.f);
             } else {
                 float4 hp = wf.hit_p[slot], hn = wf.hit_n[slot];
@@ -279,8 +279,10 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
                     shade_hit_ineept<kind>(s, rp, in, rec, rnd, out);
                 else
                     shade_hit_rpt<kind>(s, rp, in, rec, bounce, rnd, out);
-                if (out.add.x != 0.f || out.add.y != 0.f || out.add.z != 0.f)
+                if (out.add.x != 0.f || out.add.y != 0.f || out.add.z != 0.f) { // rare: the sum is read only then
+                    const float4 acc = wf.sum[slot];
                     wf.sum[slot] = make_float4(acc.x + out.add.x, acc.y + out.add.y, acc.z + out.add.z, 0.f);
+                }
                 if (out.want_nee) {
                     wf.nee_w[slot] = f4(out.W, __int_as_float(out.mat_kind));
                     mask |= 1u;

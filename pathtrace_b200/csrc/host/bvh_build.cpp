@@ -78,6 +78,8 @@ int build_range(BuildCtx &c, int begin, int end, Box &out_box, int depth)
     // SAH may produce long chains (nested shells); past this depth fall back to balanced median splits so that
     // total depth stays below the traversal stack (PT_STACK_DEPTH = 48): 24 + log2(n)
     if (n > 2 && depth < 24) {
+        // as many bins as there are boxes, at most kBins: half of all nodes hold four boxes or fewer
+        const int bins = std::min(kBins, std::max(4, n));
         double best_cost = std::numeric_limits<double>::infinity();
         int best_axis = -1, best_bin = -1;
         for (int axis = 0; axis < 3; axis++) {
@@ -86,15 +88,15 @@ int build_range(BuildCtx &c, int begin, int end, Box &out_box, int depth)
                 continue;
             Box bin_box[kBins];
             int bin_count[kBins];
-            for (int b = 0; b < kBins; b++) {
+            for (int b = 0; b < bins; b++) {
                 bin_box[b].reset();
                 bin_count[b] = 0;
             }
-            const double scale = kBins / ((double)hi - lo);
+            const double scale = bins / ((double)hi - lo);
             for (int i = begin; i < end; i++) {
                 int p = c.order[i];
                 int b = (int)(((double)c.centroid[3 * p + axis] - lo) * scale);
-                b = std::max(0, std::min(kBins - 1, b));
+                b = std::max(0, std::min(bins - 1, b));
                 bin_box[b].grow(c.prim[p]);
                 bin_count[b]++;
             }
@@ -103,7 +105,7 @@ int build_range(BuildCtx &c, int begin, int end, Box &out_box, int depth)
             Box acc;
             acc.reset();
             int cnt = 0;
-            for (int b = kBins - 1; b > 0; b--) {
+            for (int b = bins - 1; b > 0; b--) {
                 acc.grow(bin_box[b]);
                 cnt += bin_count[b];
                 right_area[b] = acc.area();
@@ -111,7 +113,7 @@ int build_range(BuildCtx &c, int begin, int end, Box &out_box, int depth)
             }
             acc.reset();
             cnt = 0;
-            for (int b = 0; b < kBins - 1; b++) {
+            for (int b = 0; b < bins - 1; b++) {
                 acc.grow(bin_box[b]);
                 cnt += bin_count[b];
                 if (cnt == 0 || right_count[b + 1] == 0)
@@ -126,10 +128,10 @@ int build_range(BuildCtx &c, int begin, int end, Box &out_box, int depth)
         }
         if (best_axis >= 0) {
             float lo = cbounds.lo[best_axis], hi = cbounds.hi[best_axis];
-            const double scale = kBins / ((double)hi - lo);
+            const double scale = bins / ((double)hi - lo);
             auto it = std::partition(c.order.begin() + begin, c.order.begin() + end, [&](int p) {
                 int b = (int)(((double)c.centroid[3 * p + best_axis] - lo) * scale);
-                b = std::max(0, std::min(kBins - 1, b));
+                b = std::max(0, std::min(bins - 1, b));
                 return b <= best_bin;
             });
             mid = (int)(it - c.order.begin());

@@ -1,26 +1,39 @@
 #include "json.h"
 
+#include <cstdint>
 #include <cstdlib>
 #include <cstring>
 
 namespace b200pt {
 
 static const Json g_null;
+static const std::vector<Json> g_no_items;
 
-const Json &Json::operator[](const std::string &key) const
+const Json *Json::find(const char *key) const
 {
     if (type_ != Object)
-        return g_null;
-    auto it = object_.find(key);
-    return it == object_.end() ? g_null : it->second;
+        return nullptr;
+    const Json *found = nullptr;
+    for (const auto &m : *object_)
+        if (m.first == key)
+            found = &m.second; // a repeated key: the last one counts, as in nlohmann
+    return found;
+}
+
+const Json &Json::operator[](const char *key) const
+{
+    const Json *j = find(key);
+    return j ? *j : g_null;
 }
 
 const Json &Json::at(size_t i) const
 {
-    if (type_ != Array || i >= array_.size())
+    if (type_ != Array || i >= array_->size())
         throw std::runtime_error("json: array index out of range");
-    return array_[i];
+    return (*array_)[i];
 }
+
+const std::vector<Json> &Json::items() const { return type_ == Array ? *array_ : g_no_items; }
 
 double Json::as_double() const
 {
@@ -44,7 +57,7 @@ const std::string &Json::as_string() const
 {
     if (type_ != String)
         throw std::runtime_error("json: value is not a string");
-    return string_;
+    return *string_;
 }
 
 class JsonParser {
@@ -88,7 +101,7 @@ private:
         if (c == '"') {
             Json v;
             v.type_ = Json::String;
-            v.string_ = parse_string();
+            v.string_.reset(new std::string(parse_string()));
             return v;
         }
         if (c == 't' || c == 'f' || c == 'n')
@@ -118,6 +131,62 @@ private:
     Json parse_number()
     {
         const char *begin = s_.c_str() + i_;
+        // Plain decimals (every number of a scene file) without strtod: with at most 15 significant digits the
+        // mantissa is exact in a double, 10^|e| is exact up to 22, so one multiplication or division gives the
+        // correctly rounded value -- the same bits strtod returns.  Anything else goes to strtod.
+        {
+            const char *p = begin;
+            const bool neg = *p == '-';
+            if (neg)
+                p++;
+            uint64_t mant = 0;
+            int digits = 0, exp10 = 0;
+            const char *first = p;
+            while (*p >= '0' && *p <= '9') {
+                mant = mant * 10 + (uint64_t)(*p - '0');
+                digits += (mant != 0);
+                p++;
+            }
+            bool ok = p != first;
+            if (*p == '.') {
+                p++;
+                const char *frac = p;
+                while (*p >= '0' && *p <= '9') {
+                    mant = mant * 10 + (uint64_t)(*p - '0');
+                    digits += (mant != 0);
+                    exp10--;
+                    p++;
+                }
+                ok = ok && p != frac;
+            }
+            if (ok && (*p == 'e' || *p == 'E')) {
+                const char *q = p + 1;
+                const bool eneg = *q == '-';
+                if (*q == '-' || *q == '+')
+                    q++;
+                int e = 0;
+                const char *efirst = q;
+                while (*q >= '0' && *q <= '9' && e < 1000) {
+                    e = e * 10 + (*q - '0');
+                    q++;
+                }
+                if (q == efirst || (*q >= '0' && *q <= '9'))
+                    ok = false;
+                exp10 += eneg ? -e : e;
+                p = q;
+            }
+            if (ok && digits <= 15 && exp10 >= -22 && exp10 <= 22) {
+                static const double pow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                                                 1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+                double d = (double)mant;
+                d = exp10 < 0 ? d / pow10[-exp10] : d * pow10[exp10];
+                i_ += (size_t)(p - begin);
+                Json v;
+                v.type_ = Json::Number;
+                v.number_ = neg ? -d : d;
+                return v;
+            }
+        }
         char *end = nullptr;
         double d = strtod(begin, &end);
         if (end == begin)
@@ -179,6 +248,7 @@ private:
     {
         Json v;
         v.type_ = Json::Array;
+        v.array_.reset(new std::vector<Json>());
         i_++;
         skip_ws();
         if (i_ < s_.size() && s_[i_] == ']') {
@@ -186,7 +256,7 @@ private:
             return v;
         }
         while (true) {
-            v.array_.push_back(parse_value());
+            v.array_->push_back(parse_value());
             skip_ws();
             if (i_ >= s_.size())
                 fail("unterminated array");
@@ -207,6 +277,7 @@ private:
     {
         Json v;
         v.type_ = Json::Object;
+        v.object_.reset(new Json::Members());
         i_++;
         skip_ws();
         if (i_ < s_.size() && s_[i_] == '}') {
@@ -222,7 +293,7 @@ private:
             if (i_ >= s_.size() || s_[i_] != ':')
                 fail("expected :");
             i_++;
-            v.object_[key] = parse_value();
+            v.object_->emplace_back(std::move(key), parse_value());
             skip_ws();
             if (i_ >= s_.size())
                 fail("unterminated object");

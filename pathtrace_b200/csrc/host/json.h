@@ -3,19 +3,28 @@
 // behaviour the two formats rely on is provided here: objects, arrays, numbers, strings, booleans,
 // null; `contains`, `value(key, default)`, `at(i)`, numeric conversion of ints to floats and back.
 #pragma once
-#include <map>
+#include <cstring>
 #include <memory>
 #include <stdexcept>
 #include <string>
+#include <utility>
 #include <vector>
 
 namespace b200pt {
 
+// A value is 40 bytes: a number lives in the value itself, strings / arrays / objects behind a pointer.  Objects keep
+// their members in file order and are searched linearly (the two formats have at most a dozen keys per object); a
+// scene file of 8192 instances is ~100 000 values.
 class Json {
 public:
     enum Type { Null, Bool, Number, String, Array, Object };
+    using Members = std::vector<std::pair<std::string, Json>>;
 
-    Json() : type_(Null) {}
+    Json() = default;
+    Json(Json &&) = default;
+    Json &operator=(Json &&) = default;
+    Json(const Json &) = delete;
+    Json &operator=(const Json &) = delete;
     static Json parse(const std::string &text);
 
     Type type() const { return type_; }
@@ -25,12 +34,14 @@ public:
     bool is_string() const { return type_ == String; }
     bool is_null() const { return type_ == Null; }
 
-    bool contains(const std::string &key) const { return type_ == Object && object_.count(key) > 0; }
+    bool contains(const char *key) const { return find(key) != nullptr; }
+    bool contains(const std::string &key) const { return find(key.c_str()) != nullptr; }
     // operator[] on a missing key yields null (nlohmann would insert null on a non-const json).
-    const Json &operator[](const std::string &key) const;
+    const Json &operator[](const char *key) const;
+    const Json &operator[](const std::string &key) const { return (*this)[key.c_str()]; }
     const Json &at(size_t i) const;
-    size_t size() const { return type_ == Array ? array_.size() : (type_ == Object ? object_.size() : 0); }
-    const std::vector<Json> &items() const { return array_; }
+    size_t size() const { return type_ == Array ? array_->size() : (type_ == Object ? object_->size() : 0); }
+    const std::vector<Json> &items() const;
 
     double as_double() const;
     float as_float() const { return (float)as_double(); }
@@ -38,22 +49,37 @@ public:
     bool as_bool() const;
     const std::string &as_string() const;
 
-    double value(const std::string &key, double dflt) const { return contains(key) ? (*this)[key].as_double() : dflt; }
-    long value(const std::string &key, long dflt) const { return contains(key) ? (*this)[key].as_int() : dflt; }
-    long value(const std::string &key, int dflt) const { return value(key, (long)dflt); }
-    bool value(const std::string &key, bool dflt) const { return contains(key) ? (*this)[key].as_bool() : dflt; }
-    std::string value(const std::string &key, const char *dflt) const
+    double value(const char *key, double dflt) const
     {
-        return contains(key) ? (*this)[key].as_string() : std::string(dflt);
+        const Json *j = find(key);
+        return j ? j->as_double() : dflt;
+    }
+    long value(const char *key, long dflt) const
+    {
+        const Json *j = find(key);
+        return j ? j->as_int() : dflt;
+    }
+    long value(const char *key, int dflt) const { return value(key, (long)dflt); }
+    bool value(const char *key, bool dflt) const
+    {
+        const Json *j = find(key);
+        return j ? j->as_bool() : dflt;
+    }
+    std::string value(const char *key, const char *dflt) const
+    {
+        const Json *j = find(key);
+        return j ? j->as_string() : std::string(dflt);
     }
 
 private:
-    Type type_;
+    const Json *find(const char *key) const;
+
+    Type type_ = Null;
     bool bool_ = false;
     double number_ = 0.0;
-    std::string string_;
-    std::vector<Json> array_;
-    std::map<std::string, Json> object_;
+    std::unique_ptr<std::string> string_;
+    std::unique_ptr<std::vector<Json>> array_;
+    std::unique_ptr<Members> object_;
     friend class JsonParser;
 };
 

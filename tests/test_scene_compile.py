@@ -151,3 +151,32 @@ def test_png_textures_decode_like_lodepng(tmp_path):
     assert [im.shape for im in flat["images"]] == [(8, 16, 4), (16, 32, 4)]
     kinds = [t["kind"] for t in flat["textures"]]
     assert kinds.count(3) == 2 and flat["textures"][flat["background"]]["kind"] == 3
+
+
+def test_json_numbers_are_correctly_rounded():
+    """json.cpp reads plain decimals without strtod (mantissa and power of ten both exact in a double -> one
+    correctly rounded operation); everything else goes to strtod.  Either way the value must be the one Python's
+    float() -- also correctly rounded -- gives for the same literal."""
+    import random
+    import pathtrace_b200 as pt
+    rnd = random.Random(5)
+    lits = ["0", "-0.0", "1", "0.1", "0.7", "25.0", "1e-7", "1E+5", "123456789012345", "1234567890123456789",
+            "0.000000000000000000001", "3.141592653589793238462643", "1e22", "1e23", "1e-22", "1e-23", "4.35e-320",
+            "17976931348623157e292", "0.30000000000000004", "9007199254740993", "5e-1", "100000000000000000000000"]
+    for _ in range(300):
+        m, e = rnd.randrange(10 ** rnd.randrange(1, 19)), rnd.randrange(-30, 30)
+        lits += [f"{m}e{e}", f"{m // 1000}.{m % 1000:03d}", f"-0.{m:018d}", f"{m}.{m}E{e:+d}"]
+    lits = lits[:len(lits) // 3 * 3]
+    mats = ",".join('{"id": "m%d", "type": "lambertian", "data": {"color": [%s, %s, %s]}}' % (k, *lits[3 * k:3 * k + 3])
+                    for k in range(len(lits) // 3))
+    text = ('{"camera": {"look_from": [0, 0, -5], "look_at": [0, 0, 0], "fov": 40, "aperture": 0, "dist_to_focus": 5},'
+            ' "world": {"color": [0, 0, 0]}, "assets": [], "textures": [], "materials": [' + mats + '], "primitives": [],'
+            ' "instances": [{"type": "direct", "primitive": {"type": "sphere", "material": {"id": "m0"}, "radius": 1}}]}')
+    sc = pt.Scene.from_json(text, 8, 8, device=-1)
+    d = sc.describe()  # a lambertian's colour becomes a constant texture
+    got = np.array([d["textures"][m["texture"]]["color"] for m in d["materials"]], dtype=np.float32).ravel()
+    sc.close()
+    with np.errstate(over="ignore"):
+        want = np.array([float(s) for s in lits], dtype=np.float64).astype(np.float32)
+    assert got.shape == want.shape
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), [l for l, g, w in zip(lits, got, want) if g != w][:5]

@@ -1,5 +1,5 @@
 #!/bin/bash
-# Run on the GPU box (gpurun -- 'bash tools/capture_profiles.sh r1g'): the bench line, the ncu launch list of the same
+# Run on the GPU box (gpurun -- 'bash tools/capture_profiles.sh r1k'): the bench line, the ncu launch list of the same
 # command and `--set full` captures of the dominant kernels, all into gpurun_out/<tag>_*.
 # tools/ncu_summary.py / tools/ncu_lines.py turn them into the text summaries committed under profiles/.
 set -u
