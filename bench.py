@@ -178,7 +178,7 @@ def scene_upload_bytes(scene):
     """Bytes b200pt_scene_create_from_json copies host -> device (capi.cu upload_scene)."""
     d = scene.desc()
     n_nodes = scene.bvh_info()["n_nodes"]
-    return (n_nodes * 64 + d.n_instances * (80 + 48) + d.n_materials * 32 + d.n_textures * 32 + d.n_lights * 4
+    return (n_nodes * 128 + d.n_instances * (80 + 48) + d.n_materials * 32 + d.n_textures * 32 + d.n_lights * 4
             + 768 * 4 * 2)
 
 
@@ -195,7 +195,17 @@ def traversal_roofline(prof_time, prof_count, peaks):
     achieved = bytes_total / secs / 1e9 if secs > 0 else 0.0
     peak = peaks["hbm_gbs"]
     share = ms[top] / max(1e-12, sum(ms.values()))
+
+    def one(kernel, pre):  # the same figures for either traversal kernel
+        r, b, p = prof_count[pre + "_rays"], prof_count[pre + "_boxes"], prof_count[pre + "_prims"]
+        t = ms[kernel] * 1e-3
+        by = 32.0 * b + 80.0 * p + 48.0 * r
+        return {"rays": r, "boxes_per_ray": round(b / max(1, r), 3), "prims_per_ray": round(p / max(1, r), 3),
+                "bytes_per_ray": round(by / max(1, r), 1), "grays_per_s": round(r / t / 1e9, 3) if t > 0 else 0.0,
+                "achieved": round(by / t / 1e9, 1) if t > 0 else 0.0, "frac": round(by / t / 1e9 / peak, 4) if t > 0 else 0.0}
+
     return {
+        "traversal_kernels": {"k_extend": one("extend", "ext"), "k_nee": one("nee", "nee")},
         "bound": "hbm", "kernel": "k_nee" if top == "nee" else "k_extend", "achieved": achieved, "peak": peak,
         "unit": "GB/s", "frac": achieved / peak, "peak_source": peaks["source"], "traffic": peaks.get("traffic"),
         "algorithmic_bytes_per_launch": bytes_total / launches, "avg_launch_ms": ms[top] / launches,
