@@ -407,6 +407,17 @@ PT_HD void hit_uv(const PtSceneView &s, int inst, int face, V3 o, V3 d, float t,
     local_uv<true>(I, xform_point(I.inv, o), xform_vector(I.inv, d), t, face, u, v);
 }
 
+// -DPT_DEBUG_BOUNDS: range checks of every node, instance and stack index on the device (tools/variants_smoke.py)
+#if defined(PT_DEBUG_BOUNDS) && defined(__CUDA_ARCH__)
+#define PT_CHECK(cond)                                                                                                 \
+    do {                                                                                                               \
+        if (!(cond))                                                                                                   \
+            __trap();                                                                                                  \
+    } while (0)
+#else
+#define PT_CHECK(cond) ((void)0)
+#endif
+
 struct TraceCounters {
     uint32_t boxes, prims;
 };
@@ -458,6 +469,7 @@ struct Traversal {
     // one that is hit, push the others farthest first.  Returns false when the traversal is complete.
     template <bool COUNT, bool SORT = true> PT_HD bool node_step(const PtSceneView &s, TraceCounters *counters)
     {
+        PT_CHECK(cur >= 0 && cur < s.n_nodes);
         const PtNode4 *node = s.nodes + cur;
         float e[4];
         int32_t ref[4];
@@ -514,12 +526,14 @@ struct Traversal {
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-        for (int k = 3; k >= 1; k--)
+        for (int k = 3; k >= 1; k--) {
+            PT_CHECK(!(e[k] < never) || sp < PT_STACK_DEPTH);
             if (e[k] < never && sp < PT_STACK_DEPTH) {
                 stack_ref[sp] = ref[k];
                 stack_t[sp] = e[k];
                 sp++;
             }
+        }
         cur = ref[0];
         return true;
     }
@@ -530,6 +544,7 @@ struct Traversal {
     template <bool COUNT, bool MEDIA, bool ANY = false>
     PT_HD bool leaf_test(const PtSceneView &s, int idx, const MediumRng &mr, TraceCounters *counters)
     {
+        PT_CHECK(idx >= 0 && idx < s.n_inst);
         InstanceData I;
         load_instance(s.inst, idx, I);
         if (ANY && meta_emitter(I.meta))
