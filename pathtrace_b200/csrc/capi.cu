@@ -165,25 +165,60 @@ class BlockCache {
     size_t dev_bytes_ = 0, pinned_bytes_ = 0;
 };
 
-// memcpy into caller memory that has often never been touched (a fresh numpy array): page faults dominate, and they
-// scale with threads
-void parallel_memcpy(void *dst, const void *src, size_t bytes)
+// Device -> pinned staging -> caller memory in 4 MB pieces: the host threads copy piece i out of the staging buffer
+// while the DMA engine is still filling the pieces behind it.  Caller memory has often never been touched (a fresh
+// numpy array): page faults dominate the host copy, and they scale with threads.
+cudaError_t copy_out_pipelined(void *dst, void *stage, const void *d_src, size_t bytes, cudaStream_t stream)
 {
-    const size_t chunk = (size_t)4 << 20;
-    unsigned n = (unsigned)std::min<size_t>((bytes + chunk - 1) / chunk, std::min(8u, std::max(1u, std::thread::hardware_concurrency())));
+    const size_t piece = (size_t)4 << 20;
+    const size_t n = (bytes + piece - 1) / piece;
     if (n <= 1) {
-        memcpy(dst, src, bytes);
-        return;
+        cudaError_t e = cudaMemcpyAsync(stage, d_src, bytes, cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess)
+            e = cudaStreamSynchronize(stream);
+        if (e == cudaSuccess)
+            memcpy(dst, stage, bytes);
+        return e;
     }
-    std::vector<std::thread> pool;
-    const size_t per = ((bytes / n) + 4095) & ~(size_t)4095;
-    for (unsigned t = 0; t < n; t++) {
-        const size_t a = std::min(bytes, per * t), b = std::min(bytes, per * (t + 1));
-        if (b > a)
-            pool.emplace_back([=] { memcpy((char *)dst + a, (const char *)src + a, b - a); });
+    std::vector<cudaEvent_t> ev(n, nullptr);
+    cudaError_t err = cudaSuccess;
+    size_t issued = 0;
+    for (; issued < n && err == cudaSuccess; issued++) {
+        const size_t off = issued * piece, len = std::min(piece, bytes - off);
+        err = cudaEventCreateWithFlags(&ev[issued], cudaEventDisableTiming);
+        if (err == cudaSuccess)
+            err = cudaMemcpyAsync((char *)stage + off, (const char *)d_src + off, len, cudaMemcpyDeviceToHost, stream);
+        if (err == cudaSuccess)
+            err = cudaEventRecord(ev[issued], stream);
     }
-    for (auto &th : pool)
-        th.join();
+    if (err == cudaSuccess) {
+        const unsigned nt = (unsigned)std::min<size_t>(n, std::min(8u, std::max(1u, std::thread::hardware_concurrency())));
+        std::vector<cudaError_t> errs(nt, cudaSuccess);
+        std::vector<std::thread> pool;
+        for (unsigned t = 0; t < nt; t++)
+            pool.emplace_back([&, t] {
+                for (size_t i = t; i < n; i += nt) {
+                    const cudaError_t e = cudaEventSynchronize(ev[i]);
+                    if (e != cudaSuccess) {
+                        errs[t] = e;
+                        return;
+                    }
+                    const size_t off = i * piece, len = std::min(piece, bytes - off);
+                    memcpy((char *)dst + off, (const char *)stage + off, len);
+                }
+            });
+        for (auto &th : pool)
+            th.join();
+        for (cudaError_t e : errs)
+            if (e != cudaSuccess)
+                err = e;
+    } else {
+        cudaStreamSynchronize(stream); // let the copies that were issued finish before the staging block is reused
+    }
+    for (cudaEvent_t e : ev)
+        if (e)
+            cudaEventDestroy(e);
+    return err;
 }
 
 int sm_count(int device)
@@ -802,11 +837,7 @@ int b200pt_render_read(b200pt_render *r, float *rgb_sums, int64_t *spp_done)
             r->d_rgbf = render_alloc<float>(*r, npix * 3);
         pt::launch_pack_rgb(r->film.accum, (int)npix, r->d_rgbf, r->scene->stream);
         void *stage = block_cache().pinned_get(bytes);
-        cudaError_t e = cudaMemcpyAsync(stage, r->d_rgbf, bytes, cudaMemcpyDeviceToHost, r->scene->stream);
-        if (e == cudaSuccess)
-            e = cudaStreamSynchronize(r->scene->stream);
-        if (e == cudaSuccess)
-            parallel_memcpy(rgb_sums, stage, bytes);
+        cudaError_t e = copy_out_pipelined(rgb_sums, stage, r->d_rgbf, bytes, r->scene->stream);
         block_cache().pinned_put(stage, bytes);
         CK(e);
         if (spp_done)

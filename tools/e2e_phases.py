@@ -7,7 +7,7 @@ import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-import pathtrace_b200 as pt  # noqa: E402
+import pathtrace_b200 as pt  # noqa: E402  (B200PT_LIB selects another build of the library)
 
 name = sys.argv[1] if len(sys.argv) > 1 else "cornell_box"
 w, h, spp = (3840, 2160, 4) if name == "book2_final" else (1024, 1024, 16)
