@@ -490,6 +490,25 @@ int b200pt_config_from_json(const char *config_json, b200pt_config *out, char *s
     });
 }
 
+// The parsed document of a large scene is ~100 000 small heap blocks; they are freed on a helper thread while the
+// caller's thread packs and uploads (joined before the entry point returns).
+#ifndef PT_DOM_ASYNC_BYTES
+#define PT_DOM_ASYNC_BYTES (64 << 10)
+#endif
+struct DomRelease {
+    std::thread worker;
+    DomRelease(Json &&doc, size_t text_bytes)
+    {
+        if (text_bytes >= (size_t)PT_DOM_ASYNC_BYTES) // a small document is freed faster than a thread starts
+            worker = std::thread([d = std::move(doc)]() mutable { Json gone(std::move(d)); });
+    }
+    ~DomRelease()
+    {
+        if (worker.joinable())
+            worker.join();
+    }
+};
+
 int b200pt_scene_create_from_json(const char *scene_json, int32_t film_width, int32_t film_height, int32_t device,
                                   b200pt_scene **out)
 {
@@ -499,7 +518,9 @@ int b200pt_scene_create_from_json(const char *scene_json, int32_t film_width, in
     return guarded([&] {
         std::unique_ptr<b200pt_scene> sc(new b200pt_scene);
         sc->device = device;
-        sc->flat = compile_scene(Json::parse(scene_json), film_width, film_height);
+        Json doc = Json::parse(scene_json);
+        sc->flat = compile_scene(doc, film_width, film_height);
+        DomRelease release(std::move(doc), strlen(scene_json));
         upload_scene(*sc);
         *out = sc.release();
     });
@@ -522,7 +543,10 @@ int b200pt_scene_create_from_file(const char *scene_path, int32_t film_width, in
         const std::string dir = slash == std::string::npos ? std::string(".") : path.substr(0, slash);
         std::unique_ptr<b200pt_scene> sc(new b200pt_scene);
         sc->device = device;
-        sc->flat = compile_scene(Json::parse(ss.str().c_str()), film_width, film_height, dir);
+        const std::string text = ss.str();
+        Json doc = Json::parse(text);
+        sc->flat = compile_scene(doc, film_width, film_height, dir);
+        DomRelease release(std::move(doc), text.size());
         upload_scene(*sc);
         *out = sc.release();
     });

@@ -283,6 +283,7 @@ BuiltBvh build_bvh(const std::vector<Aabb> &boxes)
         build_range(c, 0, n, root, 0);
     }
     out.nodes = std::move(c.nodes);
+    out.n_leaves = n;
     out.max_depth = c.max_depth;
     out.nodes4.reserve(out.nodes.size() / 2 + 1);
     collapse_node(out.nodes, 0, out.nodes4, 0, out.max_depth4, out.max_stack4);

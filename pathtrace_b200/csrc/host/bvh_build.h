@@ -12,6 +12,7 @@ struct BuiltBvh {
     int max_depth4 = 0;
     int max_stack4 = 0; // pending entries a traversal of nodes4 can need at most
     int max_depth = 0;
+    int n_leaves = 0; // instances the tree was built over
     float bounds[6] = {0, 0, 0, 0, 0, 0};
 };
 

@@ -3,6 +3,7 @@
 #include "../../../include/b200pt.h"
 #include "json.h"
 
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -17,6 +18,8 @@ struct ImageData { // image_texture (image.h:7-70)
     std::vector<float> rgba; // 4 * width * height
 };
 
+struct BuiltBvh;
+
 struct FlatScene {
     std::vector<b200pt_instance> instances;
     std::vector<b200pt_material> materials;
@@ -29,6 +32,9 @@ struct FlatScene {
     std::vector<ImageData> images;     // B200PT_TEX_IMAGE textures refer to these by index (texture.odd)
     mutable std::vector<b200pt_image> image_views; // desc() scratch: views into `images`
     std::vector<std::string> warnings; // parser warnings the reference prints to stdout
+    // compile_scene builds the tree of a large scene on a second thread while it replays the reference's instance
+    // order; pack_scene takes it from here (null: pack_scene builds it)
+    std::shared_ptr<const BuiltBvh> prebuilt_bvh;
 
     b200pt_scene_desc desc() const;
     static FlatScene from_desc(const b200pt_scene_desc &d);

@@ -249,6 +249,7 @@ private:
         Json v;
         v.type_ = Json::Array;
         v.array_.reset(new std::vector<Json>());
+        v.array_->reserve(4); // most arrays are vec3s: one allocation instead of three
         i_++;
         skip_ws();
         if (i_ < s_.size() && s_[i_] == ']') {
@@ -278,6 +279,7 @@ private:
         Json v;
         v.type_ = Json::Object;
         v.object_.reset(new Json::Members());
+        v.object_->reserve(4);
         i_++;
         skip_ws();
         if (i_ < s_.size() && s_[i_] == '}') {

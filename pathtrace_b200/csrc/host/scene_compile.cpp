@@ -2,13 +2,16 @@
 // (scene_parser.h:241-595) without building any object graph: every quirk that changes what gets
 // rendered is kept and cited; the output is plain arrays for upload.
 #include "flat_scene.h"
+#include "bvh_build.h"
 
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <exception>
 #include <functional>
 #include <map>
 #include <random>
+#include <thread>
 #include <stdexcept>
 
 namespace b200pt {
@@ -559,22 +562,23 @@ struct SortCtx {
     const Aabb *boxes;
     int axis;
 };
-thread_local SortCtx g_sort_ctx;
 
 // box_{x,y,z}_compare (bvh.h:71-131): never returns 0
-int ref_box_compare(const void *a, const void *b)
+int ref_box_compare(const void *a, const void *b, void *ctx)
 {
+    const SortCtx &c = *(const SortCtx *)ctx;
     long ia = *(const long *)a, ib = *(const long *)b;
-    float d = g_sort_ctx.boxes[ia].lo[g_sort_ctx.axis] - g_sort_ctx.boxes[ib].lo[g_sort_ctx.axis];
+    float d = c.boxes[ia].lo[c.axis] - c.boxes[ib].lo[c.axis];
     return d < 0.0 ? -1 : 1;
 }
 
 void ref_bvh_walk(RefRng &rng, const std::vector<Aabb> &boxes, long *l, int n, std::vector<int> &dup)
 {
     int axis = int(3 * rng()); // bvh.h:135
-    g_sort_ctx.boxes = boxes.data();
-    g_sort_ctx.axis = axis > 2 ? 2 : axis;
-    qsort(l, n, sizeof(long), ref_box_compare); // same libc qsort, same element size (a pointer) as bvh.h:137-148
+    SortCtx ctx{boxes.data(), axis > 2 ? 2 : axis};
+    // glibc's qsort IS qsort_r with a null argument: same algorithm, same element size (a pointer) as bvh.h:137-148,
+    // hence the same permutation -- ties included, which the never-zero comparator leaves to the algorithm
+    qsort_r(l, n, sizeof(long), ref_box_compare, &ctx);
     if (n == 1) {
         dup[l[0]] = 1; // left = right = l[0] (bvh.h:150-153)
     } else if (n > 2) {
@@ -620,8 +624,25 @@ void replay_reference_rng(FlatScene &scene)
         boxes[i] = instance_bounds(scene.instances[i]);
         order[i] = i;
     }
+    // the tree the kernels walk does not depend on the order of the instance table, only its leaf labels do: for a
+    // large scene it is built on a second thread meanwhile, over the build-order boxes, and relabelled below
+    std::shared_ptr<BuiltBvh> built;
+    std::exception_ptr build_error;
+    std::thread builder;
+    if (n >= 1024)
+        builder = std::thread([&] {
+            try {
+                built = std::make_shared<BuiltBvh>(build_bvh(boxes));
+            } catch (...) {
+                build_error = std::current_exception();
+            }
+        });
     if (n > 0)
-        ref_bvh_walk(rng, boxes, order.data(), n, dup);
+        ref_bvh_walk(rng, boxes, order.data(), n, dup); // qsort and recursion only: does not throw
+    if (builder.joinable())
+        builder.join();
+    if (build_error)
+        std::rethrow_exception(build_error);
     // `order` now lists the instances as the leaves of the reference tree, left to right.  bvh_node::hit keeps the
     // RIGHT child's record when both children report the same t (bvh.h:57-60), so among exactly coincident
     // surfaces (a box standing on the floor) the right-most leaf wins.  The instance table is stored in that
@@ -639,6 +660,20 @@ void replay_reference_rng(FlatScene &scene)
     scene.instances.swap(sorted);
     for (int32_t &l : scene.lights)
         l = new_index[l];
+    if (built) {
+        auto relabel = [&](int32_t &ref) {
+            if (ref < 0)
+                ref = ~new_index[~ref];
+        };
+        for (pt::PtNode &nd : built->nodes) {
+            relabel(nd.ref0);
+            relabel(nd.ref1);
+        }
+        for (pt::PtNode4 &nd : built->nodes4)
+            for (int k = 0; k < 4; k++)
+                relabel(nd.ref[k]);
+        scene.prebuilt_bvh = built;
+    }
 }
 
 FlatScene compile_scene(const Json &scene, int film_width, int film_height, const std::string &asset_dir)

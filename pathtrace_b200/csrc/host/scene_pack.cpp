@@ -67,7 +67,10 @@ PackedScene pack_scene(const FlatScene &f)
         for (size_t k = 0; k < ntex; k++)
             out.texels.push_back(pt::PtTexel{im.rgba[4 * k], im.rgba[4 * k + 1], im.rgba[4 * k + 2], im.rgba[4 * k + 3]});
     }
-    out.bvh = build_bvh(boxes);
+    if (f.prebuilt_bvh && f.prebuilt_bvh->n_leaves == n)
+        out.bvh = *f.prebuilt_bvh;
+    else
+        out.bvh = build_bvh(boxes);
     if (out.bvh.max_stack4 > PT_STACK_DEPTH)
         throw std::runtime_error("BVH too deep for the traversal stack (" + std::to_string(out.bvh.max_stack4) + " > " +
                                  std::to_string(PT_STACK_DEPTH) + " pending nodes)");
