@@ -175,8 +175,19 @@ static int trace_impl(void *scene, const float *rays, size_t n, const float *med
         mr.stage = stage_word(0, RNG_BATCH_MEDIUM, 0);
         mr.xi = medium_xi ? medium_xi[i] : -1.f;
         Hit h;
-        bool ok = shadow ? trace_shadow<false>(view, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7], mr, h, nullptr)
-                         : trace_closest<false>(view, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7], mr, h, nullptr);
+        bool ok;
+        if (shadow == 2) {
+            // no tree at all: every instance in index order (the closest hit and its tie rule do not depend on the
+            // order of the tests) -- the yardstick for the tree the product builds and walks
+            Traversal T;
+            T.init(v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7]);
+            for (int idx = 0; idx < view.n_inst; idx++)
+                T.leaf_test<false, true>(view, idx, mr, nullptr);
+            ok = T.result<true>(view, h);
+        } else {
+            ok = shadow ? trace_shadow<false>(view, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7], mr, h, nullptr)
+                        : trace_closest<false>(view, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7], mr, h, nullptr);
+        }
         b200pt_hit &o = hits[i];
         memset(&o, 0, sizeof(o));
         o.instance = -1;
@@ -200,6 +211,11 @@ int pt_oracle_trace(void *scene, const float *rays, size_t n, const float *mediu
 int pt_oracle_trace_shadow(void *scene, const float *rays, size_t n, const float *medium_xi, b200pt_hit *hits)
 {
     return trace_impl(scene, rays, n, medium_xi, hits, 1);
+}
+
+int pt_oracle_trace_linear(void *scene, const float *rays, size_t n, const float *medium_xi, b200pt_hit *hits)
+{
+    return trace_impl(scene, rays, n, medium_xi, hits, 2);
 }
 
 // emitter flag of every instance (n_inst bytes); returns n_inst

@@ -113,6 +113,7 @@ class PortOracle:
         self.lib.pt_oracle_last_error.restype = C.c_char_p
         self.lib.pt_oracle_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
         self.lib.pt_oracle_trace_shadow.argtypes = self.lib.pt_oracle_trace.argtypes
+        self.lib.pt_oracle_trace_linear.argtypes = self.lib.pt_oracle_trace.argtypes
         self.lib.pt_oracle_emitters.argtypes = [C.c_void_p, C.c_void_p]
         self.lib.pt_oracle_render.argtypes = [C.c_void_p, C.POINTER(_CConfig), C.c_void_p, C.c_void_p, C.c_void_p,
                                               C.POINTER(C.c_int64), C.c_int, C.c_int64, C.c_int64]
@@ -148,6 +149,15 @@ class PortOracle:
         hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
         xi = None if medium_xi is None else np.ascontiguousarray(medium_xi, dtype=np.float32)
         self.lib.pt_oracle_trace_shadow(self.h, rays.ctypes.data, rays.shape[0],
+                                        None if xi is None else xi.ctypes.data, hits.ctypes.data)
+        return hits
+
+    def trace_linear(self, rays, medium_xi=None):
+        """World::hit without any tree: every instance tested in index order."""
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+        hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
+        xi = None if medium_xi is None else np.ascontiguousarray(medium_xi, dtype=np.float32)
+        self.lib.pt_oracle_trace_linear(self.h, rays.ctypes.data, rays.shape[0],
                                         None if xi is None else xi.ctypes.data, hits.ctypes.data)
         return hits
 

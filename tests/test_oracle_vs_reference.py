@@ -118,3 +118,58 @@ def test_shadow_query_equals_filtered_closest_hit(name):
     assert np.array_equal((shadow["instance"] >= 0)[ok], lit[ok])
     for f in ("instance", "t", "p", "n"):
         assert np.array_equal(shadow[f][lit], full[f][lit]), f
+
+
+@pytest.mark.parametrize("n,seed", [(2, 1), (3, 2), (17, 3), (18, 4), (19, 5), (33, 6), (100, 7), (1000, 8), (3000, 9)])
+def test_tree_walk_equals_linear_walk_on_random_scenes(n, seed):
+    """The 4-wide tree (bvh_build.cpp collapse of the binned-SAH binary tree; >= 1024 instances: built on a second
+    thread and relabelled) and its traversal (culling with the widened limit, stack, tie rule) against no tree at all:
+    every instance tested in index order.  Bit-equal records, media included (same variate per ray)."""
+    import pathtrace_b200 as pt
+    import random_scenes
+    text = random_scenes.random_scene(n, seed)
+    oracle = PortOracle(text, 64, 36)
+    flat = pt.Scene.from_json(text, 64, 36, device=-1)
+    b = flat.bvh_info()["bounds"]
+    rays = np.concatenate([raygen.random_rays(b[:3], b[3:], 6000, seed=seed),
+                           raygen.camera_rays({k: flat.describe()["camera"][k] for k in
+                                               ("origin", "lower_left", "horizontal", "vertical")}, 64, 36)])
+    first = oracle.trace(rays[:3000], np.full(3000, 0.5, np.float32))
+    rays = np.concatenate([rays, raygen.secondary_rays(first, 3000, seed=seed + 100)])
+    xi = np.random.default_rng(seed).uniform(0.01, 0.99, len(rays)).astype(np.float32)
+    tree, lin = oracle.trace(rays, xi), oracle.trace_linear(rays, xi)
+    ok = ~(np.isnan(tree["t"]) | np.isnan(lin["t"]))  # rays in a rect's plane: order dependent (DESIGN.md 2)
+    assert ok.mean() > 0.999
+    assert (tree["instance"] >= 0).mean() > 0.2
+    for f in ("instance", "t", "p", "n", "u", "v"):
+        assert np.array_equal(tree[f][ok], lin[f][ok]), f
+    oracle.close()
+    flat.close()
+
+
+@pytest.mark.parametrize("n,seed", [(40, 11), (300, 12)])
+def test_random_scene_hits_match_live_reference(n, seed, tmp_path):
+    """The same random scenes through the UNMODIFIED reference's world->hit (rotations, nested shells, rects lying in
+    the floor plane: the tie rule on a tree that is not one of the shipped scenes')."""
+    if not have_ref_driver():
+        pytest.skip("oracle/_ref/ref_driver not built")
+    import pathtrace_b200 as pt
+    import random_scenes
+    text = random_scenes.random_scene(n, seed, media=False)
+    path = tmp_path / "random.json"
+    path.write_text(text)
+    sc = pt.Scene.from_json(text, W, H, device=-1)
+    flat = sc.describe()
+    mapping, worst = scene_match.match_leaves(RefDriver.scene(str(path), W, H), flat)
+    assert worst < 1e-6
+    b = sc.bvh_info()["bounds"]
+    rays = raygen.random_rays(b[:3], b[3:], 20000, seed=seed)
+    oracle = PortOracle(text, W, H)
+    first = oracle.trace(rays[:5000])
+    rays = np.concatenate([rays, raygen.secondary_rays(first, 10000, seed=seed + 1)])
+    ref = scene_match.remap_ref_hits(RefDriver.hit(str(path), rays), mapping)
+    got = oracle.trace(rays)
+    st = raygen.compare_hits(ref, got)
+    assert st["id_agree"] == 1.0 and st["t_rel_max"] == 0.0 and st["n_err_max"] == 0.0 and st["p_rel_max"] == 0.0, st
+    oracle.close()
+    sc.close()
