@@ -642,8 +642,33 @@ struct Traversal {
                 const float t = fdiv(E.p[4] - oy, dy);
                 if (t < t_min || t > best_t) // rect::hit's own range test (a NaN t passes)
                     continue;
-                ok = hit_rect(plane, meta_flip(meta), E.p[0], E.p[1], E.p[2], E.p[3], E.p[4],
-                              xform_point(E.inv, o), xform_vector(E.inv, d), t_min, best_t, h);
+                if (ANY) {
+                    // occlusion walks rarely get here, and their kernel is faster with the shared routine (smaller code)
+                    ok = hit_rect(plane, meta_flip(meta), E.p[0], E.p[1], E.p[2], E.p[3], E.p[4],
+                                  xform_point(E.inv, o), xform_vector(E.inv, d), t_min, best_t, h);
+                } else {
+                    // the rest of rect::hit (primitive.h:196-222) from the two other rows, each the expression
+                    // xform_point / xform_vector evaluate: hit_rect() would redo the third row and the division
+                    const float *rx = E.inv + (plane == B200PT_PLANE_YZ ? 4 : 0);
+                    const float *rz = E.inv + (plane == B200PT_PLANE_XY ? 4 : 8);
+                    const float ox = rx[0] * o.x + rx[1] * o.y + rx[2] * o.z + rx[3];
+                    const float dx = rx[0] * d.x + rx[1] * d.y + rx[2] * d.z;
+                    const float oz = rz[0] * o.x + rz[1] * o.y + rz[2] * o.z + rz[3];
+                    const float dz = rz[0] * d.x + rz[1] * d.y + rz[2] * d.z;
+                    const float xh = ox + t * dx, zh = oz + t * dz;
+                    if (xh < E.p[0] || xh > E.p[2] || zh < E.p[1] || zh > E.p[3])
+                        continue;
+                    const float sgn = meta_flip(meta) ? -1.f : 1.f;
+                    V3 n = plane == B200PT_PLANE_XY ? v3(0.f, 0.f, sgn)
+                                                    : (plane == B200PT_PLANE_YZ ? v3(sgn, 0.f, 0.f) : v3(0.f, sgn, 0.f));
+                    // dot(local d, n): the two products with the zero components only matter when they are NaN
+                    if ((dx * 0.f + dz * 0.f) + dy * sgn > 0)
+                        n = -n;
+                    h.t = t;
+                    h.face = 0;
+                    h.n = n;
+                    ok = true;
+                }
             } else {
                 float entry;
                 if (COUNT)

@@ -24,7 +24,7 @@ struct alignas(16) PtNode {
     int32_t pad1;
 };
 
-// The tree the kernels walk: the binary tree collapsed to 4 children per node (bvh_build.cpp collapse4), stored child-
+// The tree the kernels walk: the binary tree collapsed to 4 children per node (bvh_build.cpp collapse_node), stored child-
 // major so that one 128-bit load brings the same bound of all four.  Half as many dependent node fetches per ray as
 // the binary tree, and rays of a warp agree for longer on what to do next.
 #define PT_NO_CHILD 0x7fffffff

@@ -1,4 +1,4 @@
-// scene_pack.h -- FlatScene -> the arrays the kernels read (PtInstance / PtFwd / PtNode), still in host memory.
+// scene_pack.h -- FlatScene -> the arrays the kernels read (PtInstance / PtFwd / PtNode4), still in host memory.
 #pragma once
 #include "../device/pt_scene.h"
 #include "bvh_build.h"
