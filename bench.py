@@ -273,7 +273,8 @@ def ours_arm(args):
     # rank r renders global samples [r * total_spp, (r+1) * total_spp): weak scaling, disjoint Philox streams
     cfg = base.replace(samples=total_spp, sample_offset=rank * total_spp, batch_samples=0)
     r = pt.renderer_from_config(scene, cfg).start_render()
-    batch = max(1, min((8 << 20) // npix, total_spp))  # the library's automatic wavefront batch (capi.cu)
+    target_slots = int(os.environ.get("B200PT_BATCH_SLOTS", "0")) or (32 << 20)
+    batch = max(1, min(target_slots // npix, total_spp))  # the library's automatic wavefront batch (capi.cu)
     batches_per_step = -(-spp_step // batch)
     assert spp_step % batch == 0 or batch > spp_step, "a step must be a whole number of wavefront batches"
     if batch > spp_step:

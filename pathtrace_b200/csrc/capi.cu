@@ -711,7 +711,10 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         if (npix > (1ll << 30))
             throw std::runtime_error("film too large");
         // batch sizing: enough paths in flight to fill 148 SMs many times over, small enough to stay a few GB
-        const long long target_slots = 8ll << 20;
+        long long target_slots = 32ll << 20;
+        if (const char *e = std::getenv("B200PT_BATCH_SLOTS")) // tuning aid: paths in flight per wavefront batch
+            if (std::atoll(e) > 0)
+                target_slots = std::atoll(e);
         int bs = c.batch_samples > 0 ? c.batch_samples : (int)std::max<long long>(1, target_slots / npix);
         bs = std::min(bs, c.samples);
         // slots (and slots x light_samples, the NEE index space) are 32-bit indices

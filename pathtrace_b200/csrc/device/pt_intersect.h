@@ -452,8 +452,17 @@ struct Traversal {
         sp = 0;
     }
 
-    PT_HD bool pop()
+    // ANY (occlusion walk): best_t does not shrink before the walk ends, so an entry that passed the slab test
+    // when it was pushed passes it now -- its entry distance is neither stored nor compared.
+    template <bool ANY = false> PT_HD bool pop()
     {
+        if (ANY) {
+            if (sp > 0) {
+                cur = stack_ref[--sp];
+                return true;
+            }
+            return false;
+        }
         const float lim = cull_limit(best_t);
         while (sp > 0) {
             sp--;
@@ -522,7 +531,7 @@ struct Traversal {
         }
 #undef PT_CSWAP
         if (!(e[0] < never))
-            return pop();
+            return pop<!SORT>();
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
@@ -530,7 +539,8 @@ struct Traversal {
             PT_CHECK(!(e[k] < never) || sp < PT_STACK_DEPTH);
             if (e[k] < never && sp < PT_STACK_DEPTH) {
                 stack_ref[sp] = ref[k];
-                stack_t[sp] = e[k];
+                if (SORT)
+                    stack_t[sp] = e[k];
                 sp++;
             }
         }
@@ -574,7 +584,7 @@ struct Traversal {
     {
         if (leaf_test<COUNT, MEDIA, ANY>(s, ~cur, mr, counters))
             return false;
-        return pop();
+        return pop<ANY>();
     }
 
     // Shadow queries (integrator.h:246-252) need only the emission of whatever the ray meets first, and that is zero
@@ -697,7 +707,7 @@ struct Traversal {
     {
         bool more = true;
         while (more)
-            more = cur >= 0 ? node_step<COUNT>(s, counters) : leaf_step<COUNT, MEDIA, ANY>(s, mr, counters);
+            more = cur >= 0 ? node_step<COUNT, !ANY>(s, counters) : leaf_step<COUNT, MEDIA, ANY>(s, mr, counters);
     }
 
 #if defined(__CUDACC__)
@@ -723,7 +733,7 @@ struct Traversal {
             const unsigned m_in = __ballot_sync(0xffffffffu, active && cur >= 0);
             if (2 * __popc(m_in) >= __popc(m_act)) {
                 if (active && cur >= 0)
-                    active = node_step<COUNT>(s, counters);
+                    active = node_step<COUNT, !ANY>(s, counters);
             } else {
                 if (active && cur < 0)
                     active = leaf_step<COUNT, MEDIA, ANY>(s, mr, counters);
