@@ -218,6 +218,39 @@ int pt_oracle_trace_linear(void *scene, const float *rays, size_t n, const float
     return trace_impl(scene, rays, n, medium_xi, hits, 2);
 }
 
+// The horizon test k_shade uses to leave a vertex out of the NEE queue (pt_shade.h lights_below_horizon) against
+// the full computation: for n vertices (pn: n x 6 = p, normal) draw `samples` light samples each with nee_prepare.
+// out[0] = vertices the test rejects, out[1] = samples of rejected vertices that are NOT void (must be 0),
+// out[2] = vertices the test keeps although all their samples are void (what the test misses; informational).
+int pt_oracle_horizon_check(void *scene, const float *pn, size_t n, int samples, uint64_t *out)
+{
+    OracleScene *sc = (OracleScene *)scene;
+    const PtSceneView &view = sc->view;
+    out[0] = out[1] = out[2] = 0;
+    for (size_t i = 0; i < n; i++) {
+        const V3 p = v3(pn[6 * i], pn[6 * i + 1], pn[6 * i + 2]), nrm = v3(pn[6 * i + 3], pn[6 * i + 4], pn[6 * i + 5]);
+        const bool rejected = lights_below_horizon(view, p, nrm);
+        RngKey key;
+        key.seed_lo = 17, key.seed_hi = 0;
+        key.pixel = (uint32_t)i;
+        key.sample = 0;
+        int live = 0;
+        for (int k = 0; k < samples; k++) {
+            NeeSample ns;
+            nee_prepare(view, key, 0, k, p, nrm, B200PT_MAT_LAMBERTIAN, v3(1.f, 1.f, 1.f), ns);
+            if (!nee_is_void(ns))
+                live++;
+        }
+        if (rejected) {
+            out[0]++;
+            out[1] += (uint64_t)live;
+        } else if (live == 0) {
+            out[2]++;
+        }
+    }
+    return 0;
+}
+
 // emitter flag of every instance (n_inst bytes); returns n_inst
 int pt_oracle_emitters(void *scene, uint8_t *flags)
 {

@@ -321,6 +321,7 @@ void upload_scene(b200pt_scene &sc)
     v.tex = (up(sc.flat.textures));
     v.lights = (up(sc.flat.lights));
     v.emitters = (up(sc.packed.emitters));
+    v.light_boxes = (up(sc.packed.light_boxes));
     v.images = (up(sc.packed.images));
     v.texels = (up(sc.packed.texels));
     v.small = (up(sc.packed.small));

@@ -238,6 +238,7 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
         const int i = base + threadIdx.x;
         unsigned mask = 0;
         int slot = 0;
+        bool nee_skipped = false;
         if (i < n) {
             slot = q_in[i];
             float4 ro = wf.ray_o[slot], rd = wf.ray_d[slot], bt = wf.beta[slot];
@@ -284,8 +285,14 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
                     wf.sum[slot] = make_float4(acc.x + out.add.x, acc.y + out.add.y, acc.z + out.add.z, 0.f);
                 }
                 if (out.want_nee) {
-                    wf.nee_w[slot] = f4(out.W, __int_as_float(out.mat_kind));
-                    mask |= 1u;
+                    // all lights below the horizon of this vertex: its light samples are all void (pt_shade.h), they
+                    // are counted (k_tally) and never queued
+                    if (NEE && !CORR && lights_below_horizon(s, rec.p, rec.n)) {
+                        nee_skipped = true;
+                    } else {
+                        wf.nee_w[slot] = f4(out.W, __int_as_float(out.mat_kind));
+                        mask |= 1u;
+                    }
                 }
                 if (out.cont) {
                     wf.ray_o[slot] = f4(out.o, out.last_bsdf_pdf);
@@ -298,6 +305,11 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
         }
         if (kind == SK_MISS)
             continue; // uniform: a miss never appends
+        if (NEE && !CORR) {
+            const unsigned b = __ballot_sync(0xffffffffu, nee_skipped);
+            if (b && (threadIdx.x & 31) == 0)
+                atomicAdd(row + CNT_NEE_SKIP, __popc(b));
+        }
         int pos[2];
         block_reserve<2>(mask, counter, pos);
         if (mask & 1u)
@@ -468,7 +480,10 @@ __global__ void k_tally(RenderParams rp, Wavefront wf, int n_rows)
         unsigned long long hits = n_ext - (unsigned long long)row[CNT_KIND0 + SK_MISS];
         ext += n_ext;
         if (rp.integrator == B200PT_INTEGRATOR_INEEPT) {
-            shadow += (unsigned long long)row[CNT_NEE] * (unsigned long long)rp.light_samples;
+            const unsigned long long skipped = (unsigned long long)row[CNT_NEE_SKIP] * (unsigned long long)rp.light_samples;
+            shadow += (unsigned long long)row[CNT_NEE] * (unsigned long long)rp.light_samples + skipped;
+            if (wf.trace_counts)
+                wf.trace_counts[3] += skipped; // work counters: these queries cost no box and no primitive test
             ref += n_ext + hits * (unsigned long long)rp.light_samples; // integrator.h:192,247
         } else if (b > 0) {
             ref += n_ext; // one count per scatter (integrator.h:45)

@@ -48,6 +48,7 @@ struct alignas(16) PtInstance {
 // index order by the 32 lanes together (pt_intersect.h run_small), each behind the slab test of its leaf box
 // (PtBox, 32 B).  The kernels keep boxes, instances and forward transforms of such a scene in shared memory.
 #define PT_SMALL_MAX 16
+#define PT_MAX_LIGHT_BOXES 8
 struct alignas(16) PtBox {
     float lo[3];
     float pad0;
@@ -95,6 +96,7 @@ struct PtSceneView {
     const int32_t *lights;
     const PtBox *small;         // n_small leaf boxes, index = instance index; n_small == 0: use the BVH
     const int32_t *emitters;    // instances whose hit material emits (shadow rays test these first, pt_intersect.h)
+    const PtBox *light_boxes;   // world bounds of lights[0..n_light_boxes), see lights_below_horizon (pt_shade.h)
     const PtImage *images;
     const PtTexel *texels;
     const float *perlin_ranvec; // 256 x 3
@@ -103,6 +105,7 @@ struct PtSceneView {
     int32_t emit_needs_n; // some emitter is one-sided: shadow hits must report the normal (material.h:215-222)
     int32_t emit_needs_p; // some emitter has a non-constant texture: shadow hits must report p (else only the normal)
     int32_t n_media; // instances wrapped in a constant_medium; 0 selects the kernels compiled without that branch
+    int32_t n_light_boxes; // n_lights when every light is a rect or a sphere (and there are <= 8), else 0
     PtCamera cam;
 };
 

@@ -350,6 +350,31 @@ PT_HD void nee_prepare(const PtSceneView &s, const RngKey &key, int bounce, int 
     out.coef = c;
 }
 
+// Every light sample of a vertex is void (nee_is_void) when all lights lie below the vertex's horizon: the sampled
+// direction points at a point of the light (rect::random, sphere::random), n . dir is then at most the largest
+// n . (corner - p) over the corners of the light's world bounds, cos_l <= 0 and the coefficient is 0 (or NaN) for any
+// material (`dropoff`, integrator.h:240).  The margin (1e-4 of the sum of the term magnitudes, against rounding of
+// ~1e-6 in the computed cos_l) keeps the test conservative: a vertex it rejects has no sample that the full
+// computation would keep, so the film does not change.  NaNs in p or n fail the comparison: no skip.
+PT_HD bool lights_below_horizon(const PtSceneView &s, V3 p, V3 n)
+{
+    if (s.n_light_boxes == 0)
+        return false;
+    for (int l = 0; l < s.n_light_boxes; l++) {
+        const PtBox &b = s.light_boxes[l];
+        float m = 0.f, mag = 0.f;
+        const float pp[3] = {p.x, p.y, p.z}, nn[3] = {n.x, n.y, n.z};
+        for (int k = 0; k < 3; k++) {
+            const float a = nn[k] * (b.lo[k] - pp[k]), c = nn[k] * (b.hi[k] - pp[k]);
+            m += fmaxf(a, c);
+            mag += fmaxf(fabsf(a), fabsf(c));
+        }
+        if (!(m < -1e-4f * mag))
+            return false;
+    }
+    return true;
+}
+
 // a sample whose coefficient is zero or NaN contributes nothing whatever its shadow ray meets (nee_finish turns
 // a NaN product into zero): no ray needs tracing.  The reference's ray counter still counts it (k_tally).
 PT_HD bool nee_is_void(const NeeSample &ns)

@@ -17,7 +17,7 @@ namespace pt {
 enum ShadeKind { SK_MISS = 0, SK_DIFFUSE = 1, SK_DIELECTRIC = 2, SK_LIGHT = 3, SK_ISOTROPIC = 4, SK_COUNT = 5 };
 
 // counters row layout (int32 each)
-enum { CNT_EXT = 0, CNT_KIND0 = 1 /* ..5 */, CNT_NEE = 6, CNT_ROW = 8 };
+enum { CNT_EXT = 0, CNT_KIND0 = 1 /* ..5 */, CNT_NEE = 6, CNT_NEE_SKIP = 7 /* vertices whose samples are all void */, CNT_ROW = 8 };
 
 struct BatchCtl {           // device-resident, advanced by the tally kernel at the end of every batch
     int64_t sample_base;    // first global sample index of the current batch

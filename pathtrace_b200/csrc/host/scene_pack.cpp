@@ -57,6 +57,26 @@ PackedScene pack_scene(const FlatScene &f)
         boxes[i] = instance_bounds(src);
     }
     out.n_media = media;
+    // World bounds of the lights, for the horizon test of pt_shade.h lights_below_horizon: only lights whose samples
+    // point AT them (rect::random, sphere::random); a box or medium in the light list samples the fixed direction
+    // (1, 0, 0) (hittable.h:28) and switches the test off.
+    if (!f.lights.empty() && f.lights.size() <= PT_MAX_LIGHT_BOXES) {
+        bool ok = true;
+        for (int32_t li : f.lights) {
+            const b200pt_instance &src = f.instances[li];
+            if ((src.flags & B200PT_INST_MEDIUM) || (src.prim_kind != B200PT_PRIM_RECT && src.prim_kind != B200PT_PRIM_SPHERE))
+                ok = false;
+        }
+        if (ok)
+            for (int32_t li : f.lights) {
+                pt::PtBox b{};
+                for (int k = 0; k < 3; k++) {
+                    b.lo[k] = boxes[li].lo[k];
+                    b.hi[k] = boxes[li].hi[k];
+                }
+                out.light_boxes.push_back(b);
+            }
+    }
     for (const ImageData &im : f.images) {
         pt::PtImage pi{};
         pi.width = im.width;
@@ -111,6 +131,8 @@ pt::PtSceneView PackedScene::host_view(const FlatScene &f) const
     v.texels = texels.data();
     v.n_images = (int)images.size();
     v.emitters = emitters.data();
+    v.light_boxes = light_boxes.data();
+    v.n_light_boxes = (int)light_boxes.size();
     v.small = small.data();
     v.n_small = (int)small.size();
     v.n_emitters = (int)emitters.size();

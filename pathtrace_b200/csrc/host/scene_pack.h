@@ -18,6 +18,7 @@ struct PackedScene {
     std::vector<pt::PtImage> images;     // image textures: dimensions + offset into texels
     std::vector<pt::PtTexel> texels;
     std::vector<int32_t> emitters;     // instances whose hit material is a diffuse_light, ascending
+    std::vector<pt::PtBox> light_boxes; // world bounds per light (flat.lights order); empty: the horizon test is off
     int n_media = 0;
     // a view whose pointers refer to THIS object's host vectors and to `flat`'s material/texture/light arrays
     pt::PtSceneView host_view(const FlatScene &flat) const;

@@ -161,6 +161,15 @@ class PortOracle:
                                         None if xi is None else xi.ctypes.data, hits.ctypes.data)
         return hits
 
+    def horizon_check(self, points, normals, samples=16):
+        """(vertices the horizon test rejects, their samples that are not void [must be 0], kept vertices whose
+        samples are all void) -- pt_shade.h lights_below_horizon against nee_prepare."""
+        pn = np.ascontiguousarray(np.concatenate([points, normals], axis=1), dtype=np.float32)
+        out = np.zeros(3, dtype=np.uint64)
+        self.lib.pt_oracle_horizon_check.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
+        self.lib.pt_oracle_horizon_check(self.h, pn.ctypes.data, pn.shape[0], samples, out.ctypes.data)
+        return int(out[0]), int(out[1]), int(out[2])
+
     def emitters(self):
         n = self.lib.pt_oracle_emitters(self.h, None)
         flags = np.zeros(n, dtype=np.uint8)

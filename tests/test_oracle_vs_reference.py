@@ -173,3 +173,52 @@ def test_random_scene_hits_match_live_reference(n, seed, tmp_path):
     assert st["id_agree"] == 1.0 and st["t_rel_max"] == 0.0 and st["n_err_max"] == 0.0 and st["p_rel_max"] == 0.0, st
     oracle.close()
     sc.close()
+
+
+def _horizon_vertices(oracle, bounds, seed):
+    """Vertices as k_shade sees them (hit points with their normals, primary and secondary) plus adversarial ones:
+    the same points with random normals, and normals turned to lie within 1e-3 .. 1e-7 of a light's horizon."""
+    rng = np.random.default_rng(seed)
+    first = oracle.trace(raygen.random_rays(bounds[:3], bounds[3:], 30000, seed=seed), np.full(30000, 0.5, np.float32))
+    second = oracle.trace(raygen.secondary_rays(first, 30000, seed=seed + 1), np.full(30000, 0.5, np.float32))
+    hits = np.concatenate([first[first["instance"] >= 0], second[second["instance"] >= 0]])
+    hits = hits[~(np.isnan(hits["p"]).any(axis=1) | np.isnan(hits["n"]).any(axis=1))]
+    p, n = hits["p"].astype(np.float32), hits["n"].astype(np.float32)
+    rnd = rng.normal(size=p.shape).astype(np.float32)
+    rnd /= np.linalg.norm(rnd, axis=1, keepdims=True)
+    # normals nearly perpendicular to the direction of a point near the scene centre's lights: n = unit(t + eps * d)
+    target = p[rng.integers(0, len(p), len(p))]  # some other surface point (lights are among them)
+    d = target - p
+    d /= np.maximum(np.linalg.norm(d, axis=1, keepdims=True), 1e-20)
+    t = np.cross(d, rnd)
+    t /= np.maximum(np.linalg.norm(t, axis=1, keepdims=True), 1e-20)
+    eps = (10.0 ** rng.uniform(-7, -3, size=(len(p), 1)) * rng.choice([-1.0, 1.0], size=(len(p), 1))).astype(np.float32)
+    graze = (t + eps * d).astype(np.float32)
+    return np.concatenate([p, p, p]), np.concatenate([n, rnd, graze])
+
+
+@pytest.mark.parametrize("name", SCENE_FILES)
+def test_horizon_test_only_rejects_vertices_without_live_light_samples(name):
+    """k_shade leaves a vertex out of the NEE queue when every light lies below its horizon
+    (pt_shade.h lights_below_horizon).  That must never drop a sample the full computation (nee_prepare: light
+    pick, rect::random / sphere::random, cos_l, pdfs, MIS weight -- integrator.h:221-244) would keep."""
+    oracle = PortOracle.from_file(scene_path(name), W, H)
+    b = _flat(name).bvh_info()["bounds"]
+    p, n = _horizon_vertices(oracle, b, seed=31)
+    rejected, live_in_rejected, missed = oracle.horizon_check(p, n, samples=16)
+    assert live_in_rejected == 0
+    if name != "cornell_box_image_textures":
+        assert rejected > 0.05 * len(p), "the test never fires on this scene"
+    # what it misses is small: vertices kept although all 16 samples came out void
+    assert missed < 0.2 * len(p), (rejected, missed, len(p))
+
+
+@pytest.mark.parametrize("n_inst,seed", [(18, 4), (100, 7), (1000, 8)])
+def test_horizon_test_on_random_scenes(n_inst, seed):
+    import random_scenes
+    text = random_scenes.random_scene(n_inst, seed)
+    oracle = PortOracle(text, W, H)
+    flat = __import__("pathtrace_b200").Scene.from_json(text, W, H, device=-1)
+    p, n = _horizon_vertices(oracle, flat.bvh_info()["bounds"], seed=seed)
+    rejected, live_in_rejected, missed = oracle.horizon_check(p, n, samples=16)
+    assert live_in_rejected == 0, (rejected, live_in_rejected)
