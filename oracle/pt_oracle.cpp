@@ -180,6 +180,8 @@ static int trace_impl(void *scene, const float *rays, size_t n, const float *med
             // no tree at all: every instance in index order (the closest hit and its tie rule do not depend on the
             // order of the tests) -- the yardstick for the tree the product builds and walks
             Traversal T;
+            TraversalStack T_stack;
+            T.stk = &T_stack;
             T.init(v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6], q[7]);
             for (int idx = 0; idx < view.n_inst; idx++)
                 T.leaf_test<false, true>(view, idx, mr, nullptr);

@@ -167,7 +167,10 @@ __global__ void __launch_bounds__(kThreads) k_raygen(PtSceneView s, RenderParams
 #endif
 constexpr int kExtThreads = PT_EXT_THREADS;
 template <bool COUNT, bool MEDIA, bool SMALL>
-__global__ void __launch_bounds__(kExtThreads) k_extend(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
+#ifndef PT_EXT_MINB
+#define PT_EXT_MINB 16
+#endif
+__global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
     __shared__ SmallScene s_small; // dropped by the compiler when SMALL is false
     if (SMALL)
@@ -187,6 +190,8 @@ __global__ void __launch_bounds__(kExtThreads) k_extend(PtSceneView s, RenderPar
         int slot = 0;
         const bool live = i < n;
         Traversal T;
+        TraversalStack T_stack;
+        T.stk = SMALL ? nullptr : &T_stack; // the table walk of a small scene has no pending nodes
         MediumRng mr;
         mr.xi = -1.f;
         if (live) {
@@ -349,6 +354,8 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
         V3 c = v3(0.f, 0.f, 0.f);
         int slot = -1;
         Traversal T;
+        TraversalStack T_stack;
+        T.stk = SMALL ? nullptr : &T_stack; // the table walk of a small scene has no pending nodes
         MediumRng mr;
         mr.xi = -1.f;
         NeeSample ns;
@@ -514,6 +521,8 @@ __global__ void __launch_bounds__(kThreads) k_trace_batch(PtSceneView s, const f
         const size_t i = base + threadIdx.x;
         const bool live = i < n;
         Traversal T;
+        TraversalStack T_stack;
+        T.stk = SMALL ? nullptr : &T_stack; // the table walk of a small scene has no pending nodes
         MediumRng mr;
         mr.xi = -1.f;
         TraceCounters tc;

@@ -427,6 +427,11 @@ struct TraceCounters {
 // World::hit (world.h:17-20) as a resumable state machine: init() -> steps until one returns false -> result().
 // A step visits one inner node (node_step) or tests one leaf (leaf_step).  The CPU restatement runs a ray to
 // completion (run / trace_closest); the kernels run 32 rays per warp and vote on the kind of step (run_warp).
+struct TraversalStack {
+    int32_t ref[PT_STACK_DEPTH];
+    float t[PT_STACK_DEPTH];
+};
+
 struct Traversal {
     V3 o, d, inv_d;
     float t_min, best_t;
@@ -434,8 +439,10 @@ struct Traversal {
     PrimHit best;
     int32_t cur; // node to visit next: >= 0 inner node, < 0 leaf (~instance)
     int32_t sp;
-    int32_t stack_ref[PT_STACK_DEPTH];
-    float stack_t[PT_STACK_DEPTH];
+    // The pending-node stack is an object of its own (attach it before init): inside this struct, every store to
+    // stack_ref[sp] might have overwritten sp or the ray as far as the compiler could tell, and the whole state was
+    // kept in local memory and re-read after each push.
+    TraversalStack *stk;
 
     PT_HD void init(V3 origin, V3 dir, float tmin, float tmax)
     {
@@ -458,7 +465,7 @@ struct Traversal {
     {
         if (ANY) {
             if (sp > 0) {
-                cur = stack_ref[--sp];
+                cur = stk->ref[--sp];
                 return true;
             }
             return false;
@@ -466,8 +473,8 @@ struct Traversal {
         const float lim = cull_limit(best_t);
         while (sp > 0) {
             sp--;
-            if (stack_t[sp] <= lim) {
-                cur = stack_ref[sp];
+            if (stk->t[sp] <= lim) {
+                cur = stk->ref[sp];
                 return true;
             }
         }
@@ -538,9 +545,9 @@ struct Traversal {
         for (int k = 3; k >= 1; k--) {
             PT_CHECK(!(e[k] < never) || sp < PT_STACK_DEPTH);
             if (e[k] < never && sp < PT_STACK_DEPTH) {
-                stack_ref[sp] = ref[k];
+                stk->ref[sp] = ref[k];
                 if (SORT)
-                    stack_t[sp] = e[k];
+                    stk->t[sp] = e[k];
                 sp++;
             }
         }
@@ -810,6 +817,8 @@ PT_HD bool trace_closest(const PtSceneView &s, V3 o, V3 d, float t_min, float t_
                          TraceCounters *counters)
 {
     Traversal T;
+    TraversalStack T_stack;
+    T.stk = &T_stack;
     T.init(o, d, t_min, t_max);
     if (s.n_small > 0)
         T.template run_small<COUNT, MEDIA>(s.small, s.inst, s.n_small, mr, counters);
@@ -825,6 +834,8 @@ PT_HD bool trace_shadow(const PtSceneView &s, V3 o, V3 d, float t_min, float t_m
                         TraceCounters *counters, int known_inst = -1, const PrimHit *known = nullptr)
 {
     Traversal T;
+    TraversalStack T_stack;
+    T.stk = &T_stack;
     T.init(o, d, t_min, t_max);
     if (s.n_emitters > PT_MAX_DIRECT_EMITTERS) {
         T.template run<COUNT, MEDIA>(s, mr, counters);
