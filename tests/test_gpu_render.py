@@ -265,3 +265,23 @@ def test_degenerate_films_and_settings():
     far = _render(cfgd, sample_offset=(1 << 33) + 5)[0].framebuffer
     near = _render(cfgd, sample_offset=5)[0].framebuffer
     assert np.isfinite(far).all() and far.max() > 0 and far.shape == near.shape
+
+
+@pytest.mark.parametrize("scene", ["book2_final", "cornell_box", "light_test"])
+def test_horizon_skip_keeps_ray_accounting_and_film(scene):
+    """k_shade leaves vertices whose lights all lie below their horizon out of the NEE queue (pt_shade.h
+    lights_below_horizon).  Their shadow queries must still be counted -- in the report (`rays_shadow`, compared with
+    the CPU restatement, which has no such shortcut) and in the work counters of the profiling build -- and the
+    film must be the one the restatement computes without the shortcut."""
+    cfgd = _cfg(scene, 96, 54, 8)
+    r, rep = _render(cfgd, profile=2)
+    prof = r.profile()
+    assert prof["nee_rays"] == rep["rays_shadow"]
+    assert prof["ext_rays"] == rep["rays_extension"]
+    oracle = PortOracle.from_file(scene_path(scene), 96, 54)
+    ref = oracle.render(make_cconfig(cfgd), stats=False)
+    # a differing libm ulp can flip a Russian-roulette or medium decision on a handful of paths (as in
+    # test_render_matches_cpu_restatement); a vertex dropped without being counted would be a few per cent
+    for k in ("rays_extension", "rays_shadow", "rays_reference"):
+        assert abs(rep[k] - ref[k]) <= 2e-3 * ref[k] + 8, (k, rep[k], ref[k])
+    _close(r.framebuffer, ref["sums"], scene)
