@@ -143,7 +143,8 @@ typedef struct b200pt_config {
     uint64_t seed;          /* Philox key */
     int64_t sample_offset;  /* first global sample index rendered by this handle (spp sharding) */
     int32_t device;         /* CUDA device ordinal */
-    int32_t batch_samples;  /* samples per pixel per wavefront batch; 0 = auto */
+    int32_t batch_samples;  /* samples per pixel per wavefront batch; 0 = auto (about 32 Mi paths in flight, ~6.5 GB of state;
+                               the environment variable B200PT_BATCH_SLOTS overrides that target) */
     float stats_clamp;      /* >0: also accumulate per-pixel sum / sum of squares of the per-sample
                                radiance clamped at this value (parity statistics) */
     int32_t profile;        /* measurement aid: 1 = bracket every kernel launch with CUDA events on the render stream
