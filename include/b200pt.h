@@ -146,7 +146,8 @@ typedef struct b200pt_config {
     int32_t batch_samples;  /* samples per pixel per wavefront batch; 0 = auto (about 32 Mi paths in flight, ~6.5 GB of state;
                                the environment variable B200PT_BATCH_SLOTS overrides that target) */
     float stats_clamp;      /* >0: also accumulate per-pixel sum / sum of squares of the per-sample
-                               radiance clamped at this value (parity statistics) */
+                               radiance clamped to [-stats_clamp, stats_clamp] (parity statistics; a Perlin albedo can be
+                               negative, texture.h:191) */
     int32_t profile;        /* measurement aid: 1 = bracket every kernel launch with CUDA events on the render stream
                                (per-kernel device time), 2 = run the traversal kernels with work counters on
                                (BVH boxes / primitives tested); see b200pt_render_profile.  0 in production. */
@@ -216,6 +217,11 @@ int b200pt_trace_batch_device(b200pt_scene *scene, const void *d_rays, size_t n,
  * over rays (counts[0] = boxes, counts[1] = primitives, counts[2] = hits). HOST rays. */
 int b200pt_trace_count(b200pt_scene *scene, const float *rays, size_t n, uint64_t counts[3]);
 
+/* random_double (random.h:9-15) is replaced by Philox4x32-10 keyed (seed; pixel, global sample, bounce/stage/k, index)
+ * (device/pt_rng.h).  This runs the bare generator on the device: counters_keys = n x 6 words {counter[4], key[2]},
+ * out = n x 4 words, both in HOST memory -- for known-answer tests against the published Random123 vectors. */
+int b200pt_philox4x32_10(int32_t device, const uint32_t *counters_keys, size_t n, uint32_t *out);
+
 /* ---- render lifecycle --------------------------------------------------------------------- */
 typedef struct b200pt_progress {
     int64_t samples_done;   /* camera samples finished (pixels x spp), as Tiled::samples_done */
@@ -260,6 +266,10 @@ int b200pt_render_write_ppm(b200pt_render *render, int64_t n_samples, const char
 int b200pt_render_paths(b200pt_render *render, int32_t capacity, int32_t *n_paths, int32_t *vertices_per_path,
                         int32_t *pixel, int64_t *sample, int32_t *length, float *points);
 int b200pt_render_write_paths(b200pt_render *render, const char *path_3d, const char *path_2d, int32_t *n_paths);
+/* camera::project (camera.h:49-109) for n points (HOST, n x 3): xy receives n x 2 film coordinates, ok[i] its return
+ * value.  For a point behind the film plane (t < 0) x = y = 0 and ok = 0 only when a coordinate exceeds 1e10 -- the
+ * reference's own behaviour, which handle_traced_paths prints as "0,0!". */
+int b200pt_camera_project(const b200pt_scene *scene, const float *points, size_t n, float *xy, int32_t *ok);
 /* The string value of a top-level key of config.json (e.g. "traced_paths_output_path"); empty when absent. */
 int b200pt_config_string(const char *config_json, const char *key, char *out, size_t cap);
 

@@ -52,6 +52,7 @@ RenderParams make_params(const b200pt_config &c)
     rp.integrator = c.integrator;
     rp.max_bounces = c.max_bounces;
     rp.light_samples = c.integrator == B200PT_INTEGRATOR_INEEPT ? c.light_samples : 0;
+    rp.light_group = 0; // the lane-group size of k_nee; the scalar loop below reproduces its summation order itself
     rp.russian_roulette = c.russian_roulette;
     rp.only_direct = c.only_direct_illumination;
     rp.corrected = c.physically_corrected ? 1 : 0;
@@ -62,13 +63,13 @@ RenderParams make_params(const b200pt_config &c)
 }
 
 // one camera sample = one call of integrator->color (renderer.h:648-670)
-V3 sample_color(const PtSceneView &s, const RenderParams &rp, uint32_t pixel, uint32_t sample, SampleCounts &cnt)
+V3 sample_color(const PtSceneView &s, const RenderParams &rp, uint32_t pixel, long long sample, SampleCounts &cnt)
 {
     RngKey key;
     key.seed_lo = rp.seed_lo;
     key.seed_hi = rp.seed_hi;
     key.pixel = pixel;
-    key.sample = sample;
+    key_set_sample(key, sample);
     F4 r = rng4(key, stage_word(0, RNG_CAMERA, 0), 0);
     int j = pixel / rp.width, i = pixel - j * rp.width;
     float u = (float)(i + (double)r.x) / (float)rp.width;
@@ -110,12 +111,33 @@ V3 sample_color(const PtSceneView &s, const RenderParams &rp, uint32_t pixel, ui
         if (nee)
             cnt.reference += rp.light_samples;
         if (out.want_nee) {
+            // summed in the order of k_nee's butterfly over a lane group of P = light_samples rounded up to a power
+            // of two (pairs, pairs of pairs, ...), so that the two sums can be compared bit for bit
+            V3 v[32];
             V3 light = v3(0.f, 0.f, 0.f);
-            for (int k = 0; k < rp.light_samples; k++) {
-                light += rp.corrected ? nee_sample_corrected<false>(s, key, b, k, rec.p, rec.n, out.mat_kind, out.W, nullptr)
-                                      : nee_sample<false>(s, rp, key, b, k, rec.p, rec.n, out.mat_kind, out.W, nullptr);
-                cnt.shadow++;
+            int P = 1;
+            while (P < rp.light_samples && P < 32)
+                P *= 2;
+            const bool tree = rp.light_samples <= 32;
+            for (int k = 0; k < (tree ? P : rp.light_samples); k++) {
+                V3 c = v3(0.f, 0.f, 0.f);
+                if (k < rp.light_samples) {
+                    c = rp.corrected ? nee_sample_corrected<false>(s, key, b, k, rec.p, rec.n, out.mat_kind, out.W, nullptr)
+                                     : nee_sample<false>(s, rp, key, b, k, rec.p, rec.n, out.mat_kind, out.W, nullptr);
+                    cnt.shadow++;
+                }
+                if (tree)
+                    v[k] = c;
+                else
+                    light += c;
             }
+            if (tree) {
+                for (int off = 1; off < P; off <<= 1)
+                    for (int i = 0; i < P; i += 2 * off)
+                        v[i] = v[i] + v[i + off];
+                light = v[0];
+            }
+            // k_nee adds nothing when the group sum is exactly zero; x + 0 = x leaves the bits alone either way
             sum += light / (float)rp.light_samples;
         }
         if (!out.cont)
@@ -134,6 +156,33 @@ V3 sample_color(const PtSceneView &s, const RenderParams &rp, uint32_t pixel, ui
 extern "C" {
 
 const char *pt_oracle_last_error(void) { return g_err.c_str(); }
+
+// the bare generator of pt_rng.h (known-answer tests): n x {counter[4], key[2]} -> n x 4 words
+void pt_oracle_philox(const uint32_t *in, size_t n, uint32_t *out)
+{
+    for (size_t i = 0; i < n; i++) {
+        U4 c;
+        c.x = in[6 * i], c.y = in[6 * i + 1], c.z = in[6 * i + 2], c.w = in[6 * i + 3];
+        const U4 r = philox4x32_10(c, in[6 * i + 4], in[6 * i + 5]);
+        out[4 * i] = r.x, out[4 * i + 1] = r.y, out[4 * i + 2] = r.z, out[4 * i + 3] = r.w;
+    }
+}
+
+// the four uniforms rng4() hands out for (seed; pixel, global sample, stage word, index) and the stage word itself
+void pt_oracle_rng4(uint64_t seed, uint32_t pixel, int64_t sample, int bounce, int stage, int k, uint32_t idx, float *out4,
+                    uint32_t *stage_word_out)
+{
+    RngKey key;
+    key.seed_lo = (uint32_t)(seed & 0xffffffffull);
+    key.seed_hi = (uint32_t)(seed >> 32);
+    key.pixel = pixel;
+    key_set_sample(key, sample);
+    const uint32_t sw = stage_word(bounce, stage, k);
+    const F4 r = rng4(key, sw, idx);
+    out4[0] = r.x, out4[1] = r.y, out4[2] = r.z, out4[3] = r.w;
+    if (stage_word_out)
+        *stage_word_out = sw;
+}
 
 // asset_dir: where png textures are looked up after the working directory (may be null)
 void *pt_oracle_scene_create2(const char *scene_json, int film_w, int film_h, const char *asset_dir)
@@ -172,6 +221,7 @@ static int trace_impl(void *scene, const float *rays, size_t n, const float *med
         mr.key.seed_lo = mr.key.seed_hi = 0;
         mr.key.pixel = (uint32_t)(i & 0xffffffffull);
         mr.key.sample = (uint32_t)(i >> 32);
+        mr.key.sample_hi = 0;
         mr.stage = stage_word(0, RNG_BATCH_MEDIUM, 0);
         mr.xi = medium_xi ? medium_xi[i] : -1.f;
         Hit h;
@@ -236,6 +286,7 @@ int pt_oracle_horizon_check(void *scene, const float *pn, size_t n, int samples,
         key.seed_lo = 17, key.seed_hi = 0;
         key.pixel = (uint32_t)i;
         key.sample = 0;
+        key.sample_hi = 0;
         int live = 0;
         for (int k = 0; k < samples; k++) {
             NeeSample ns;
@@ -293,12 +344,13 @@ int pt_oracle_render(void *scene, const b200pt_config *config, float *rgb_sums, 
             for (int64_t pix = p0; pix < p1; pix++) {
                 float acc[3] = {0, 0, 0}, cs[3] = {0, 0, 0}, cq[3] = {0, 0, 0};
                 for (int sidx = 0; sidx < c.samples; sidx++) {
-                    V3 col = sample_color(sc->view, rp, (uint32_t)pix, (uint32_t)(c.sample_offset + sidx), cnt);
+                    V3 col = sample_color(sc->view, rp, (uint32_t)pix, (long long)c.sample_offset + sidx, cnt);
                     float x[3] = {is_nan(col.x) ? 0.f : col.x, is_nan(col.y) ? 0.f : col.y, is_nan(col.z) ? 0.f : col.z};
                     for (int k = 0; k < 3; k++) {
                         acc[k] += x[k];
                         if (c.stats_clamp > 0.f) {
-                            float cx = x[k] < c.stats_clamp ? x[k] : c.stats_clamp;
+                            float cx = x[k] < c.stats_clamp ? x[k] : c.stats_clamp; // two-sided: a Perlin albedo can be negative
+                            cx = cx > -c.stats_clamp ? cx : -c.stats_clamp;
                             cs[k] += cx;
                             cq[k] += cx * cx;
                         }

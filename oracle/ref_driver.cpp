@@ -14,6 +14,12 @@
 //   hit    <scene.json> <rays.f32> <out.bin> [burn]       closest hit per ray (n x 8 float32 in)
 //   color  <config.json> <out.f64> <nsamples> <clamp> [burn]   per-pixel sample statistics
 //   main   (cwd holds config.json)                        the reference's own main(), untouched
+//   film   <fb.f32> <w> <h> <n_samples> <exposure> <out.ppm> <out.json>
+//                                                         calculate_luminance (helpers.h:146-168) + output_to_file
+//                                                         (renderer.h:24-55) on a supplied framebuffer of sums
+//   project <scene.json> <film_w> <film_h> <paths.txt> <out3d.txt> <out2d.txt> <out.json>
+//                                                         camera::project (camera.h:49-109) per point and
+//                                                         handle_traced_paths (renderer.h:57-96) on supplied paths
 #define main ref_main
 #include "main.cpp"
 #undef main
@@ -342,7 +348,7 @@ static int mode_hit(int argc, char **argv)
 // Per-pixel sample statistics of integrator->color, sampled exactly as Tiled::compute does
 // (renderer.h:648-670): jittered (u,v), cam.get_ray, one draw for the trace-probability test.
 // Output (float64): header {W,H,N,clamp,total_rays}, then per pixel (row j=0 is the image BOTTOM,
-// as in the reference framebuffer): mean[3] (unclamped), cmean[3], cM2[3] (clamped at `clamp`).
+// as in the reference framebuffer): mean[3] (unclamped), cmean[3], cM2[3] (clamped to [-clamp, clamp]).
 static int mode_color(int argc, char **argv)
 {
     if (argc < 6)
@@ -384,7 +390,7 @@ static int mode_color(int argc, char **argv)
                 {
                     double x = col[c];
                     mean[c] += (x - mean[c]) / (s + 1);
-                    double xc = x > clampv ? clampv : x;
+                    double xc = x > clampv ? clampv : (x < -clampv ? -clampv : x); // two-sided: a Perlin albedo can be negative (texture.h:191)
                     double d = xc - cmean[c];
                     cmean[c] += d / (s + 1);
                     cm2[c] += d * (xc - cmean[c]);
@@ -410,11 +416,89 @@ static int mode_color(int argc, char **argv)
     return 0;
 }
 
+// The reference's film path on a framebuffer handed in by the test: fb.f32 holds H x W x 3 float32 SUMS, row 0 =
+// image bottom (the layout of Renderer::framebuffer, renderer.h:682).
+static int mode_film(int argc, char **argv)
+{
+    if (argc < 9)
+        return 2;
+    const int W = atoi(argv[3]), H = atoi(argv[4]), n = atoi(argv[5]);
+    const float exposure = (float)atof(argv[6]);
+    std::vector<float> raw((size_t)W * H * 3);
+    FILE *f = fopen(argv[2], "rb");
+    if (!f || fread(raw.data(), sizeof(float), raw.size(), f) != raw.size())
+        return 2;
+    fclose(f);
+    vec3 **fb = new vec3 *[H];
+    for (int j = 0; j < H; j++)
+    {
+        fb[j] = new vec3[W];
+        for (int i = 0; i < W; i++)
+        {
+            const float *q = &raw[((size_t)j * W + i) * 3];
+            fb[j][i] = vec3(q[0], q[1], q[2]);
+        }
+    }
+    float max_luminance = 0, total_luminance = 0, avg_luminance = 0;
+    calculate_luminance(fb, W, H, n, (long)W * H, max_luminance, total_luminance, avg_luminance);
+    auto out = std::make_shared<std::ofstream>(argv[7], std::ios::binary);
+    output_to_file(out, fb, W, H, n, max_luminance, exposure, 0.0f);
+    out->close();
+    json j;
+    j["max_luminance"] = max_luminance;
+    j["total_luminance"] = total_luminance;
+    j["avg_luminance"] = avg_luminance;
+    std::ofstream oj(argv[8]);
+    oj << std::setprecision(9) << j.dump() << std::endl;
+    return 0;
+}
+
+// paths.txt: one "x y z" per line, a blank line ends a path (an empty path is allowed: two blank lines).
+static int mode_project(int argc, char **argv)
+{
+    if (argc < 9)
+        return 2;
+    json scene = read_json(argv[2]);
+    const int W = atoi(argv[3]), H = atoi(argv[4]);
+    camera cam = setup_camera(scene["camera"], float(W) / float(H));
+    paths all;
+    path *cur = new path();
+    std::ifstream in(argv[5]);
+    std::string line;
+    json pts = json::array();
+    while (std::getline(in, line))
+    {
+        if (line.empty())
+        {
+            all.push_back(cur);
+            cur = new path();
+            continue;
+        }
+        float x, y, z;
+        if (sscanf(line.c_str(), "%g %g %g", &x, &y, &z) != 3)
+            return 2;
+        cur->push_back(vec3(x, y, z));
+        float px = 0, py = 0;
+        bool ok = cam.project(vec3(x, y, z), px, py);
+        pts.push_back(json::array({px, py, ok ? 1 : 0}));
+    }
+    if (!cur->empty())
+        all.push_back(cur);
+    int added = 0;
+    handle_traced_paths(argv[6], argv[7], cam, added, 1, &all);
+    json j;
+    j["added_paths"] = added;
+    j["projected"] = pts;
+    std::ofstream oj(argv[8]);
+    oj << std::setprecision(9) << j.dump() << std::endl;
+    return 0;
+}
+
 int main(int argc, char **argv)
 {
     if (argc < 2)
     {
-        fprintf(stderr, "usage: ref_driver scene|hit|color|main ...\n");
+        fprintf(stderr, "usage: ref_driver scene|hit|color|main|film|project ...\n");
         return 2;
     }
     if (!strcmp(argv[1], "scene"))
@@ -425,5 +509,9 @@ int main(int argc, char **argv)
         return mode_color(argc, argv);
     if (!strcmp(argv[1], "main"))
         return ref_main(argc, argv);
+    if (!strcmp(argv[1], "film"))
+        return mode_film(argc, argv);
+    if (!strcmp(argv[1], "project"))
+        return mode_project(argc, argv);
     return 2;
 }

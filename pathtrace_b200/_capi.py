@@ -99,6 +99,7 @@ SIGNATURES = {
     "b200pt_trace_batch_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int32,
                                             C.POINTER(C.c_float)]),
     "b200pt_trace_count": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_uint64)]),
+    "b200pt_philox4x32_10": (C.c_int, [C.c_int32, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200pt_render_start": (C.c_int, [C.c_void_p, C.POINTER(Config), C.POINTER(C.c_void_p)]),
     "b200pt_render_poll": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(Progress)]),
     "b200pt_render_read": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]),
@@ -110,6 +111,7 @@ SIGNATURES = {
     "b200pt_render_paths": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200pt_render_write_paths": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_int32)]),
+    "b200pt_camera_project": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]),
     "b200pt_config_string": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]),
     "b200pt_render_profile": (C.c_int, [C.c_void_p, C.POINTER(Profile)]),
     "b200pt_render_destroy": (None, [C.c_void_p]),

@@ -686,6 +686,32 @@ int b200pt_trace_count(b200pt_scene *scene, const float *rays, size_t n, uint64_
     });
 }
 
+int b200pt_philox4x32_10(int32_t device, const uint32_t *counters_keys, size_t n, uint32_t *out)
+{
+    if ((!counters_keys || !out) && n)
+        return fail(B200PT_ERR_INVALID, "null argument");
+    return guarded([&] {
+        select_device(device);
+        if (n == 0)
+            return;
+        uint32_t *d_in = nullptr, *d_out = nullptr;
+        struct Guard {
+            uint32_t *&a, *&b;
+            ~Guard()
+            {
+                cudaFree(a);
+                cudaFree(b);
+            }
+        } guard{d_in, d_out};
+        CK(cudaMalloc(&d_in, n * 6 * sizeof(uint32_t)));
+        CK(cudaMalloc(&d_out, n * 4 * sizeof(uint32_t)));
+        CK(cudaMemcpy(d_in, counters_keys, n * 6 * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        pt::launch_philox(d_in, n, d_out, nullptr);
+        CK(cudaGetLastError());
+        CK(cudaMemcpy(out, d_out, n * 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    });
+}
+
 int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt_render **out)
 {
     if (!scene || !config || !out)
@@ -702,6 +728,9 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         // integrator.h:265 divides the light sum by light_samples: with 0 every sample that reaches a surface is NaN
         if (c.integrator == B200PT_INTEGRATOR_INEEPT && (c.light_samples < 1 || c.light_samples > 1024))
             throw std::runtime_error("config: light_samples must be in [1, 1024] for \"iterative nee path tracing\"");
+        // global sample indices are keyed into Philox as 56 bits (pt_rng.h)
+        if (c.sample_offset < 0 || c.sample_offset > (1ll << PT_RNG_MAX_SAMPLE_BITS) - (long long)c.samples)
+            throw std::runtime_error("config: sample_offset must lie in [0, 2^56 - samples]");
         if (c.device != scene->device)
             throw std::runtime_error("config.device differs from the device the scene was uploaded to");
         need_device(scene);
@@ -719,7 +748,14 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         int bs = c.batch_samples > 0 ? c.batch_samples : (int)std::max<long long>(1, target_slots / npix);
         bs = std::min(bs, c.samples);
         // slots (and slots x light_samples, the NEE index space) are 32-bit indices
-        const long long per_slot = c.integrator == B200PT_INTEGRATOR_INEEPT && c.light_samples > 1 ? c.light_samples : 1;
+        // (k_nee pads the samples of a vertex to a power-of-two lane group when light_samples <= 32)
+        long long per_slot = 1;
+        if (c.integrator == B200PT_INTEGRATOR_INEEPT && c.light_samples > 1) {
+            per_slot = c.light_samples;
+            if (c.light_samples <= 32)
+                for (per_slot = 1; per_slot < c.light_samples;)
+                    per_slot *= 2;
+        }
         while ((long long)bs * npix * per_slot > (1ll << 30) && bs > 1)
             bs--;
         if ((long long)bs * npix * per_slot >= (1ll << 31))
@@ -734,6 +770,7 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         rp.integrator = c.integrator;
         rp.max_bounces = c.max_bounces;
         rp.light_samples = c.integrator == B200PT_INTEGRATOR_INEEPT ? c.light_samples : 0;
+        rp.light_group = rp.light_samples >= 1 && rp.light_samples <= 32 ? (int32_t)(rp.light_samples > 1 ? per_slot : 1) : 0;
         rp.russian_roulette = c.russian_roulette;
         rp.only_direct = c.only_direct_illumination;
         rp.corrected = c.physically_corrected ? 1 : 0;
@@ -1006,35 +1043,44 @@ std::vector<TracedPath> fetch_paths(b200pt_render &r)
     return out;
 }
 
-// camera::project (camera.h:49-109), float arithmetic as written there
+// camera::project (camera.h:49-109), float arithmetic as written there: dot() is x*x + y*y + z*z with no zero to
+// start from, which decides the SIGN of a zero denominator for a point in the camera's plane (t = +-inf)
+float dot3(const float a[3], const float b[3]) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+
 bool camera_project(const b200pt_camera &c, const float pt[3], float &x, float &y)
 {
-    float d[3], a = 0.f, b = 0.f;
+    float d[3], l[3];
     for (int k = 0; k < 3; k++) {
-        d[k] = c.origin[k] - pt[k];
-        a += (c.lower_left[k] - pt[k]) * c.w[k];
+        d[k] = c.origin[k] - pt[k];     // ray(point, origin - point)
+        l[k] = c.lower_left[k] - pt[k]; // lower_left_corner - r.origin()
     }
-    for (int k = 0; k < 3; k++)
-        b += d[k] * c.w[k];
-    const float t = a / b;
+    const float t = dot3(l, c.w) / dot3(d, c.w);
     if (t < 0.0) {
         const float lim = 1.0e+10f;
         return !(fabsf(pt[0]) > lim || fabsf(pt[1]) > lim || fabsf(pt[2]) > lim);
     }
-    float hp = 0.f, vp = 0.f, hh = 0.f, vv = 0.f;
-    for (int k = 0; k < 3; k++) {
-        const float p = pt[k] + t * d[k] - c.lower_left[k];
-        hp += c.horizontal[k] * p;
-        vp += c.vertical[k] * p;
-        hh += c.horizontal[k] * c.horizontal[k];
-        vv += c.vertical[k] * c.vertical[k];
-    }
-    x = hp / hh;
-    y = vp / vv;
+    float p[3];
+    for (int k = 0; k < 3; k++)
+        p[k] = pt[k] + t * d[k] - c.lower_left[k];
+    x = dot3(c.horizontal, p) / dot3(c.horizontal, c.horizontal);
+    y = dot3(c.vertical, p) / dot3(c.vertical, c.vertical);
     return true;
 }
 
 } // namespace
+
+int b200pt_camera_project(const b200pt_scene *scene, const float *points, size_t n, float *xy, int32_t *ok)
+{
+    if (!scene || ((!points || !xy || !ok) && n))
+        return fail(B200PT_ERR_INVALID, "null argument");
+    for (size_t i = 0; i < n; i++) {
+        float x = 0.f, y = 0.f; // the caller's initial values survive a behind-the-film point (renderer.h:76-78)
+        ok[i] = camera_project(scene->flat.camera, points + 3 * i, x, y) ? 1 : 0;
+        xy[2 * i] = x;
+        xy[2 * i + 1] = y;
+    }
+    return B200PT_OK;
+}
 
 int b200pt_render_paths(b200pt_render *r, int32_t capacity, int32_t *n_paths, int32_t *vertices_per_path, int32_t *pixel,
                         int64_t *sample, int32_t *length, float *points)

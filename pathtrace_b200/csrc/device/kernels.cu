@@ -12,6 +12,8 @@
 // intersection math, divergence and the L2/HBM traffic of the path state.
 #include "wavefront.cuh"
 
+#include <algorithm>
+
 namespace pt {
 
 namespace {
@@ -109,7 +111,7 @@ __device__ __forceinline__ RngKey make_key(const RenderParams &rp, const Wavefro
     // ~20 instructions and every kernel keys its random numbers through here
     int s_local = wf.npix_mul ? (int)(__umulhi((uint32_t)slot, wf.npix_mul) >> wf.npix_shr) : slot;
     k.pixel = (uint32_t)(slot - s_local * wf.npix);
-    k.sample = (uint32_t)(sample_base + s_local);
+    key_set_sample(k, sample_base + s_local);
     return k;
 }
 
@@ -149,8 +151,7 @@ __global__ void __launch_bounds__(kThreads) k_raygen(PtSceneView s, RenderParams
             if (rng4(key, stage_word(0, RNG_PATH_TRACE, 0), 0).x < wf.path_prob) {
                 id = atomicAdd(wf.path_count, 1);
                 if (id < wf.path_max) {
-                    const long long gs = sample_base + (long long)(key.sample - (uint32_t)sample_base);
-                    wf.path_hdr[id] = make_int4((int)key.pixel, (int)(gs & 0xffffffffll), (int)(gs >> 32), 0);
+                    wf.path_hdr[id] = make_int4((int)key.pixel, (int)key.sample, (int)key.sample_hi, 0);
                 } else {
                     id = -1;
                 }
@@ -344,10 +345,14 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
     unsigned long long nrays = 0;
     const long long sample_base = wf.ctl->sample_base;
     const int L = rp.light_samples;
-    // capacity * light_samples < 2^31 is guaranteed by b200pt_render_start (it shrinks the batch otherwise)
-    const unsigned n = (unsigned)wf.counters[bounce * CNT_ROW + CNT_NEE] * (unsigned)L;
-    const bool pow2 = (L & (L - 1)) == 0 && L <= 32;
-    const int shift = __ffs(L) - 1;
+    // The samples of one vertex occupy a group of P adjacent lanes, P = light_samples rounded up to a power of two
+    // (rp.light_group; lanes k >= L of a group idle), so that their sum is a fixed-order butterfly whatever L is.
+    // P == 0 (light_samples > 32): one thread per sample, float atomics -- the one case whose film is not
+    // bit-reproducible (include/b200pt.h).  capacity * P < 2^31 is guaranteed by b200pt_render_start.
+    const int P = rp.light_group;
+    const bool pow2 = P != 0;
+    const int shift = pow2 ? __ffs(P) - 1 : 0;
+    const unsigned n = (unsigned)wf.counters[bounce * CNT_ROW + CNT_NEE] * (unsigned)(pow2 ? P : L);
     const float inv_L_div = (float)L;
     for (unsigned base = blockIdx.x * kThreads; base < n; base += gridDim.x * kThreads) {
         const unsigned e = base + threadIdx.x;
@@ -361,15 +366,15 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
         NeeSample ns;
         bool trace = false;
         int lit = -1;
-        if (e < n) {
-            int q, k;
-            if (pow2) {
-                q = (int)(e >> shift);
-                k = (int)(e & (unsigned)(L - 1));
-            } else {
-                q = (int)(e / (unsigned)L);
-                k = (int)(e - (unsigned)q * (unsigned)L);
-            }
+        int q = 0, k = 0;
+        if (pow2) {
+            q = (int)(e >> shift);
+            k = (int)(e & (unsigned)(P - 1));
+        } else {
+            q = (int)(e / (unsigned)L);
+            k = (int)(e - (unsigned)q * (unsigned)L);
+        }
+        if (e < n && k < L) {
             slot = wf.q_nee[q];
             float4 hp = wf.hit_p[slot], hn = wf.hit_n[slot], w = wf.nee_w[slot];
             RngKey key = make_key(rp, wf, slot, sample_base);
@@ -400,8 +405,8 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
             c = CORR ? nee_finish_corrected(s, ns, hit, lrec) : nee_finish(s, ns, hit, lrec);
         }
         if (pow2) {
-            // lanes [g*L, (g+1)*L) hold one vertex (kThreads and 32 are multiples of L): fixed-order butterfly over
-            // the group.  Five unconditional stages (the stages >= L are discarded) keep the shuffles out of
+            // lanes [g*P, (g+1)*P) hold one vertex (kThreads and 32 are multiples of P): fixed-order butterfly over
+            // the group.  Five unconditional stages (the stages >= P are discarded) keep the shuffles out of
             // divergent control flow.
             __syncwarp();
 #pragma unroll
@@ -409,13 +414,13 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
                 const float x = __shfl_xor_sync(0xffffffffu, c.x, off);
                 const float y = __shfl_xor_sync(0xffffffffu, c.y, off);
                 const float z = __shfl_xor_sync(0xffffffffu, c.z, off);
-                if (off < L) {
+                if (off < P) {
                     c.x += x;
                     c.y += y;
                     c.z += z;
                 }
             }
-            if (slot >= 0 && (threadIdx.x & (L - 1)) == 0 && (c.x != 0.f || c.y != 0.f || c.z != 0.f)) {
+            if (slot >= 0 && (threadIdx.x & (P - 1)) == 0 && (c.x != 0.f || c.y != 0.f || c.z != 0.f)) {
                 // one lane per vertex and kernel touches sum[slot]: a reduction without a return value is as
                 // deterministic as load-add-store and does not wait for the load
                 float *dst = reinterpret_cast<float *>(wf.sum + slot);
@@ -458,7 +463,9 @@ __global__ void __launch_bounds__(kThreads) k_accumulate(RenderParams rp, Wavefr
             acc.y += y;
             acc.z += z;
             if (stats) {
-                float cx = fminf(x, film.clamp), cy = fminf(y, film.clamp), cz = fminf(z, film.clamp);
+                // two-sided: a Perlin albedo can be negative (texture.h:191) and the estimator has no finite variance (Q4)
+                const float lo = -film.clamp;
+                float cx = fmaxf(fminf(x, film.clamp), lo), cy = fmaxf(fminf(y, film.clamp), lo), cz = fmaxf(fminf(z, film.clamp), lo);
                 cs.x += cx;
                 cs.y += cy;
                 cs.z += cz;
@@ -534,6 +541,7 @@ __global__ void __launch_bounds__(kThreads) k_trace_batch(PtSceneView s, const f
             mr.key.seed_hi = 0;
             mr.key.pixel = (uint32_t)(i & 0xffffffffull);
             mr.key.sample = (uint32_t)(i >> 32);
+            mr.key.sample_hi = 0;
             mr.stage = stage_word(0, RNG_BATCH_MEDIUM, 0);
             mr.xi = medium_xi ? medium_xi[i] : -1.f;
             T.init(v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), b.z, b.w);
@@ -579,6 +587,17 @@ __global__ void __launch_bounds__(kThreads) k_trace_batch(PtSceneView s, const f
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+
+// the generator on its own: n x {counter[4], key[2]} -> n x 4 words (known-answer tests of pt_rng.h on the device)
+__global__ void k_philox(const uint32_t *__restrict__ in, size_t n, uint32_t *__restrict__ out)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        U4 c;
+        c.x = in[6 * i], c.y = in[6 * i + 1], c.z = in[6 * i + 2], c.w = in[6 * i + 3];
+        const U4 r = philox4x32_10(c, in[6 * i + 4], in[6 * i + 5]);
+        out[4 * i] = r.x, out[4 * i + 1] = r.y, out[4 * i + 2] = r.z, out[4 * i + 3] = r.w;
+    }
+}
 
 // calculate_luminance (helpers.h:146-168): max and total over pixels of |de_nan(sum) / n|
 __global__ void __launch_bounds__(kThreads) k_luminance(const float4 *__restrict__ accum, int npix, float inv_n,
@@ -773,6 +792,12 @@ void launch_trace_batch(const PtSceneView &s, const float *rays, size_t n, const
     else
         PT_LAUNCH_TB(false, false, nullptr);
 #undef PT_LAUNCH_TB
+}
+
+void launch_philox(const uint32_t *in, size_t n, uint32_t *out, cudaStream_t st)
+{
+    if (n)
+        k_philox<<<(unsigned)std::min<size_t>((n + 255) / 256, 148 * 8), 256, 0, st>>>(in, n, out);
 }
 
 void launch_luminance(const float4 *accum, int npix, float inv_n, float *max_total, cudaStream_t st)

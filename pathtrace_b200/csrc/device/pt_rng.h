@@ -46,7 +46,8 @@ PT_HD U4 philox4x32_10(U4 ctr, uint32_t k0, uint32_t k1)
 // 24-bit uniform in [0,1)
 PT_HD float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
 
-// stage words: (bounce << 16) | (stage << 8) | k
+// stage words: (bounce << 16) | (stage << 12) | k   with bounce < 2^16, stage < 16, k < 2^12 (k = light sample index;
+// b200pt_render_start caps light_samples at 1024 and max_bounces at 4096, so the three fields never overlap)
 enum {
     RNG_CAMERA = 0,      // idx 0: {pixel jitter u, v, lens r1, lens r2}
     RNG_EXT_MEDIUM = 1,  // idx = medium slot: {xi, xi2 (BVH-duplicated medium)}
@@ -57,12 +58,25 @@ enum {
     RNG_BATCH_MEDIUM = 5 // b200pt_trace_batch without explicit variates: (ray lo, ray hi) as (pixel, sample)
 };
 
+// The GLOBAL sample index is 64 bits wide (config.sample_offset is an int64): its low word is one counter word, its
+// high bits (at most 24: b200pt_render_start refuses offsets beyond 2^56) share the fourth counter word with `idx`
+// (< 256: half a medium slot index, or 0).  Two samples 2^32 apart draw different numbers.
 struct RngKey {
     uint32_t seed_lo, seed_hi;
     uint32_t pixel, sample;
+    uint32_t sample_hi;
 };
 
-PT_HD uint32_t stage_word(int bounce, int stage, int k) { return ((uint32_t)bounce << 16) | ((uint32_t)stage << 8) | (uint32_t)k; }
+#define PT_RNG_MAX_K 4096          /* exclusive bound of the k field of a stage word */
+#define PT_RNG_MAX_SAMPLE_BITS 56  /* global sample indices are < 2^56 */
+
+PT_HD uint32_t stage_word(int bounce, int stage, int k) { return ((uint32_t)bounce << 16) | ((uint32_t)stage << 12) | (uint32_t)k; }
+
+PT_HD void key_set_sample(RngKey &key, long long global_sample)
+{
+    key.sample = (uint32_t)((unsigned long long)global_sample & 0xffffffffull);
+    key.sample_hi = (uint32_t)((unsigned long long)global_sample >> 32);
+}
 
 PT_HD F4 rng4(const RngKey &key, uint32_t stage, uint32_t idx)
 {
@@ -70,7 +84,7 @@ PT_HD F4 rng4(const RngKey &key, uint32_t stage, uint32_t idx)
     c.x = key.pixel;
     c.y = key.sample;
     c.z = stage;
-    c.w = idx;
+    c.w = (key.sample_hi << 8) | idx;
     U4 r = philox4x32_10(c, key.seed_lo, key.seed_hi);
     F4 f;
     f.x = u01(r.x);

@@ -11,6 +11,7 @@ struct RenderParams {
     int32_t width, height;
     int32_t integrator; // B200PT_INTEGRATOR_*
     int32_t max_bounces, light_samples;
+    int32_t light_group; // light_samples rounded up to a power of two when <= 32 (k_nee's lane group), else 0
     int32_t russian_roulette, only_direct;
     int32_t corrected; // config.physically_corrected (pt_corrected.h)
     float normal_offset;

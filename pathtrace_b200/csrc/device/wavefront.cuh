@@ -83,6 +83,9 @@ void launch_accumulate(const RenderParams &rp, const Wavefront &wf, const Film &
 void launch_trace_batch(const PtSceneView &s, const float *rays, size_t n, const float *medium_xi, b200pt_hit *hits,
                         unsigned long long *counts, cudaStream_t st);
 
+// Philox4x32-10 on n x {counter[4], key[2]} words -> n x 4 words (known-answer tests)
+void launch_philox(const uint32_t *in, size_t n, uint32_t *out, cudaStream_t st);
+
 // film: luminance reduce (max, total of |sum/n|) and tonemap to bytes (top row first)
 void launch_luminance(const float4 *accum, int npix, float inv_n, float *max_total /* [2] */, cudaStream_t st);
 void launch_pack_rgb(const float4 *accum, int npix, float *rgb, cudaStream_t st);

@@ -180,6 +180,14 @@ class Scene:
                                        hits.ctypes.data))
         return hits
 
+    def project(self, points):
+        """camera::project (camera.h:49-109): (n, 3) world points -> ((n, 2) film coordinates, (n,) bool return values)."""
+        pts = np.ascontiguousarray(points, dtype=np.float32).reshape(-1, 3)
+        xy = np.zeros((pts.shape[0], 2), dtype=np.float32)
+        ok = np.zeros(pts.shape[0], dtype=np.int32)
+        check(lib().b200pt_camera_project(self._h, pts.ctypes.data, pts.shape[0], xy.ctypes.data, ok.ctypes.data))
+        return xy, ok.astype(bool)
+
     def trace_count(self, rays):
         rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
         counts = (C.c_uint64 * 3)()

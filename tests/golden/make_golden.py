@@ -30,6 +30,7 @@ from oracle_lib import PortOracle, RefDriver  # noqa: E402
 SMALL = ["three_orbs", "cornell_box", "cornell_box_small_lights", "cornell_box_with_volume", "cornell_box_with_volume2",
          "light_test", "cornell_box_image_textures"]
 ONLY = os.environ.get("GOLDEN_ONLY", "")  # regenerate only the scenes / tags containing this substring
+ONLY_EXACT = os.environ.get("GOLDEN_TAG", "")  # regenerate exactly this color tag
 ALL = SMALL + ["book2_final"]
 W, H = 32, 18
 
@@ -81,19 +82,41 @@ COLOR_CASES = {
     "light_test_b2": ("light_test", 32, 18, 2048, 3.0, dict(max_bounces=2)),
     "book2_final_b2": ("book2_final", 32, 18, 2048, 3.0, dict(max_bounces=2)),
     "cornell_box_image_textures_b2": ("cornell_box_image_textures", 32, 32, 2048, 3.0, dict(max_bounces=2)),
+    # the SHIPPED integrator settings (config.json:12-25: INEEPT, max_bounces 10, light_samples 4, RR on) on every
+    # BASELINE scene, plus one rung each with Russian roulette off and with direct illumination only.
+    # `_rep` = a second, independent replica of the reference (RNG burnt by REP_BURN draws before the scene is built):
+    # the reference-vs-reference floor the block-rRMSE of the GPU is judged against.
+    "cornell_box_full": ("cornell_box", 64, 64, 1024, 3.0, dict()),
+    "cornell_box_full_rep": ("cornell_box", 64, 64, 1024, 3.0, dict()),
+    "cornell_box_small_lights_full": ("cornell_box_small_lights", 64, 64, 1024, 3.0, dict()),
+    "cornell_box_small_lights_full_rep": ("cornell_box_small_lights", 64, 64, 1024, 3.0, dict()),
+    "cornell_box_with_volume_full": ("cornell_box_with_volume", 64, 64, 1024, 3.0, dict()),
+    "cornell_box_with_volume_full_rep": ("cornell_box_with_volume", 64, 64, 1024, 3.0, dict()),
+    "book2_final_full": ("book2_final", 64, 36, 1024, 3.0, dict()),
+    "book2_final_full_rep": ("book2_final", 64, 36, 1024, 3.0, dict()),
+    # the north star's literal sample count (4096 spp), for the "rRMSE @ 4096 spp next to the floor" report
+    "cornell_box_4096": ("cornell_box", 64, 64, 4096, 3.0, dict()),
+    "cornell_box_4096_rep": ("cornell_box", 64, 64, 4096, 3.0, dict()),
+    "cornell_box_norr": ("cornell_box", 48, 48, 1024, 3.0, dict(russian_roulette=False)),
+    "cornell_box_direct": ("cornell_box", 48, 48, 1024, 3.0, dict(only_direct_illumination=True)),
+    "cornell_box_with_volume_norr": ("cornell_box_with_volume", 32, 32, 1024, 3.0, dict(russian_roulette=False)),
 }
+REP_BURN = 10_000_019  # draws discarded by the `_rep` replicas
 
 
 def make_color():
     import pathtrace_b200 as pt
     for tag, (scene, w, h, n, clamp, over) in COLOR_CASES.items():
-        if ONLY not in tag:
+        if ONLY not in tag or (ONLY_EXACT and tag != ONLY_EXACT):
             continue
         cfgd = pt.default_config_dict(width=w, height=h, samples=n, scene=scene_file(scene), **over)
-        out = RefDriver.color(cfgd, n, clamp)
+        rep = tag.endswith("_rep")
+        out = RefDriver.color(cfgd, n, clamp, burn=REP_BURN if rep else 0)
         cfg_store = dict(cfgd, scene=f"scenes/{scene}.json")
+        big = w * h > 32 * 32  # the larger films are stored as float32 (1e-7 relative: far below their sampling noise)
+        f = (lambda a: a.astype(np.float32)) if big else (lambda a: a)
         np.savez_compressed(os.path.join(HERE, f"color_{tag}.npz"), config=json.dumps(cfg_store), n=n, clamp=clamp,
-                            mean=out["mean"], cmean=out["cmean"], cm2=out["cm2"], total_rays=out["total_rays"])
+                            mean=f(out["mean"]), cmean=f(out["cmean"]), cm2=f(out["cm2"]), total_rays=out["total_rays"])
         print("color", tag, "mean radiance", float(out["mean"].mean()), "rays", out["total_rays"])
 
 

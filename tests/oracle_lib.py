@@ -67,6 +67,46 @@ class RefDriver:
                 "cmean": body[..., 3:6], "cm2": body[..., 6:9]}
 
 
+    @staticmethod
+    def film(fb_sums, n_samples, exposure):
+        """The reference's own film path on a supplied framebuffer of sums (H x W x 3, row 0 = bottom):
+        calculate_luminance (helpers.h:146-168) + output_to_file (renderer.h:24-55).  Returns (image H x W x 3 uint8
+        with the TOP row first, max_luminance, avg_luminance, the file's bytes)."""
+        fb = np.ascontiguousarray(fb_sums, dtype=np.float32)
+        h, w, _ = fb.shape
+        with tempfile.TemporaryDirectory() as d:
+            fin, ppm, js = os.path.join(d, "fb.f32"), os.path.join(d, "out.ppm"), os.path.join(d, "out.json")
+            fb.tofile(fin)
+            subprocess.run([REF_DRIVER, "film", fin, str(w), str(h), str(int(n_samples)), repr(float(exposure)), ppm, js],
+                           check=True, cwd=ROOT, stdout=subprocess.DEVNULL)
+            with open(ppm, "rb") as f:
+                data = f.read()
+            with open(js) as f:
+                j = json.load(f)
+        header = f"P6\n{w} {h}\n255\n".encode()
+        assert data.startswith(header) and len(data) == len(header) + w * h * 3, (len(data), len(header) + w * h * 3)
+        img = np.frombuffer(data[len(header):], dtype=np.uint8).reshape(h, w, 3)
+        return img, j["max_luminance"], j["avg_luminance"], data
+
+    @staticmethod
+    def project(scene_path, w, h, paths):
+        """camera::project (camera.h:49-109) per point and handle_traced_paths (renderer.h:57-96) on the supplied paths
+        (a list of (k, 3) arrays).  Returns dict(projected = (n, 3) [x, y, ok], text3d, text2d, added_paths)."""
+        with tempfile.TemporaryDirectory() as d:
+            pin, o3, o2, js = (os.path.join(d, n) for n in ("paths.txt", "o3.txt", "o2.txt", "out.json"))
+            with open(pin, "w") as f:
+                for p in paths:
+                    for v in np.asarray(p, dtype=np.float32).reshape(-1, 3):
+                        f.write("%.9g %.9g %.9g\n" % (v[0], v[1], v[2]))
+                    f.write("\n")
+            subprocess.run([REF_DRIVER, "project", scene_path, str(w), str(h), pin, o3, o2, js], check=True, cwd=ROOT,
+                           stdout=subprocess.DEVNULL)
+            with open(js) as f:
+                j = json.load(f)
+            return {"projected": np.array(j["projected"], dtype=np.float64).reshape(-1, 3), "text3d": open(o3).read(),
+                    "text2d": open(o2).read(), "added_paths": j["added_paths"]}
+
+
 class _CConfig(C.Structure):  # mirrors b200pt_config (include/b200pt.h)
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("exposure", C.c_float), ("gamma", C.c_float),
                 ("integrator", C.c_int32), ("max_bounces", C.c_int32), ("samples", C.c_int32),

