@@ -45,7 +45,7 @@ def test_camera_project_matches_reference(name, w, h):
     assert np.array_equal(fin, np.isfinite(xy).all(axis=1))
     np.testing.assert_allclose(xy[fin], ref[fin, :2], rtol=2e-5, atol=1e-6)
     behind = (ref[:, 0] == 0) & (ref[:, 1] == 0)
-    assert behind.sum() > 100 and np.array_equal(behind, (xy[:, 0] == 0) & (xy[:, 1] == 0))  # x, y left at 0 (t < 0)
+    assert behind.sum() > 30 and np.array_equal(behind, (xy[:, 0] == 0) & (xy[:, 1] == 0))  # x, y left at 0 (t < 0)
 
 
 def _compare_film(r, fb, n):
