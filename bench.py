@@ -3,13 +3,15 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--scene NAME] [--spp-per-step S]
 
-Workload (BASELINE.json configs[1]): scenes/cornell_box.json at 1024x1024 with the shipped integrator settings
-("iterative nee path tracing", max_bounces 10, light_samples 4, Russian roulette on).  One STEP renders S samples
-per pixel of the whole film (S x 1024 x 1024 camera paths), as wavefront batches on the device; rates do not depend on
-the number of samples, so K steps of S spp stand for the config's 1024 spp (K*S = 1024 reproduces it in full).
-Multi-GPU (torchrun, one rank per GPU): every rank renders its own S-spp share of each step (spp sharding, global
-sample indices keyed into Philox), no collective on the data path; ONE NCCL sum-reduce of the film to rank 0 closes
-the timed region.  `value` = camera paths of all ranks / max-over-ranks device time -> "scaling": "weak".
+Workload (default): the north star's TARGET config, BASELINE.json configs[4] -- scenes/book2_final.json (8192 instances,
+media, BVH) at 3840x2160 with the shipped integrator settings ("iterative nee path tracing", max_bounces 10,
+light_samples 4, Russian roulette on).  It fits one GPU.  `--scene` selects any of the other four configs.
+One STEP renders a fixed TOTAL of S samples per pixel of the whole film (default 64 at 4K: 531 M camera paths), so 16
+steps are the config's 1024-spp frame; rates do not depend on the number of samples.
+Multi-GPU (torchrun, one rank per GPU): the S spp of a step are SPLIT over the ranks (spp sharding on global Philox
+sample indices, the reference's own split: renderer.h:352-360), no collective on the data path; ONE NCCL sum-reduce of
+the film to rank 0 closes the job inside the timed region.  Total work is fixed as N grows -> "scaling": "strong".
+`value` = camera paths of all ranks / max-over-ranks device time.
 
 Output: ONE JSON line (see the keys at the bottom).  `--impl reference` times the UNMODIFIED reference CPU renderer
 (oracle/_ref/ref_driver main = its own main()) on the host cores for the same scene/film/settings.
@@ -35,6 +37,8 @@ SCENES = {  # name -> (width, height, spp of the BASELINE config)
     "cornell_box_with_volume": (1024, 1024, 2048),
     "book2_final": (3840, 2160, 1024),
 }
+CONFIG_INDEX = {"three_orbs": 0, "cornell_box": 1, "cornell_box_small_lights": 2, "cornell_box_with_volume": 3,
+                "book2_final": 4}
 FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.5 TFLOP/s fp32 FMA peak at max clock
 
 
@@ -44,12 +48,14 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=16)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--scene", default="cornell_box", choices=sorted(SCENES))
-    ap.add_argument("--spp-per-step", type=int, default=0, help="0 = 16 (4 for the 4K scene)")
+    ap.add_argument("--scene", default="book2_final", choices=sorted(SCENES))
+    ap.add_argument("--spp-per-step", type=int, default=0,
+                    help="TOTAL samples per pixel of one step, split over the ranks; 0 = 64 (256 for the 1024^2 films)")
     ap.add_argument("--width", type=int, default=0)
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target length of the CPU baseline sample")
+    ap.add_argument("--cpu-one-thread", action="store_true", help="also time the reference on ONE thread (SURVEY 8d)")
     return ap.parse_args()
 
 
@@ -130,39 +136,50 @@ def run_reference_once(cfgd, spp, threads, block=32, timeout=3000):
             "mpaths_per_s": paths / secs * 1e-6, "mrays_per_s": rays / secs * 1e-6}
 
 
-def cpu_sample_spp(cfgd, threads, target_seconds):
-    """Samples per pixel for a run of about `target_seconds`: calibrated on a 1-spp run of the same film."""
+def cpu_sample(cfgd, threads, target_seconds):
+    """One bounded run of the reference on the bench film: a 1-spp probe calibrates the sample count for a run of about
+    `target_seconds`; when the probe alone is already that long (the 4K film) the probe IS the sample."""
     probe = run_reference_once(cfgd, 1, threads)
+    if probe["wall_seconds"] >= 0.6 * target_seconds:
+        return 1, probe
     rate = probe["paths"] / max(probe["wall_seconds"], 0.25)
     npix = cfgd["film"]["width"] * cfgd["film"]["height"]
-    return max(1, min(64, int(round(rate * target_seconds / npix)))), probe
+    spp = max(1, min(64, int(round(rate * target_seconds / npix))))
+    return spp, run_reference_once(cfgd, spp, threads)
+
+
+def workload_name(args, w, h):
+    return (f"{args.scene} {w}x{h}, iterative nee path tracing, max_bounces 10, light_samples 4, RR on "
+            f"(BASELINE.json configs[{CONFIG_INDEX[args.scene]}])")
 
 
 def reference_arm(args):
-    """--impl reference: K timed runs (after W warm-up runs) of the reference on all host threads."""
+    """--impl reference: timed runs of the UNMODIFIED reference main() on all host threads, each a bounded sample of the
+    bench film (whole film, few spp), the whole arm bounded to a few minutes whatever --steps asks for."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     cfgd = config_dict(args)
     threads = os.cpu_count() or 1
     w, h = cfgd["film"]["width"], cfgd["film"]["height"]
-    # a step = the whole film at `spp` samples, sized for ~10 s; K and W are capped so the arm ends within minutes
-    spp, probe = cpu_sample_spp(cfgd, threads, 10.0)
-    steps, warm = max(1, min(args.steps, 6)), max(0, min(args.warmup, 1))
-    for _ in range(warm):
-        run_reference_once(cfgd, spp, threads)
+    probe = run_reference_once(cfgd, 1, threads)  # doubles as the warm-up run
+    per_spp = max(probe["wall_seconds"], 0.25)
+    spp = max(1, min(64, int(10.0 / per_spp)))  # a step of about 10 s, at least 1 spp of the whole film
+    budget = 150.0  # seconds of timed runs
+    steps = max(1, min(args.steps, int(budget / (per_spp * spp))))
+    warm = 1
     runs = [run_reference_once(cfgd, spp, threads) for _ in range(steps)]
     paths = sum(r["paths"] for r in runs)
     secs = sum(r["seconds"] for r in runs)
     rays = sum(r["rays"] for r in runs)
     value = paths / secs * 1e-6
-    sample = f"{args.scene} {w}x{h} at {spp} spp per step, tiled 32x32 blocks, unmodified reference main()"
+    sample = (f"{args.scene} {w}x{h} at {spp} spp per step x {steps} steps (bounded: --steps {args.steps} asked), tiled "
+              f"32x32 blocks, {threads} threads, unmodified reference main(); rates as it prints them (renderer.h:705-706)")
     line = {
         "impl": "reference", "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": secs / steps * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.scene} {w}x{h}, iterative nee path tracing, max_bounces 10, light_samples 4, RR on",
-                   "spp_per_step": spp, "steps_requested": args.steps},
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args, w, h), "spp_per_step": spp, "steps_requested": args.steps},
         "mrays_per_s": rays / secs * 1e-6, "rays_per_path": rays / paths,
         "cpu_baseline": {"value": value, "unit": "Mpaths/s", "cores": threads, "kind": "reference", "sample": sample},
         "e2e": {"value": value, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -182,40 +199,57 @@ def scene_upload_bytes(scene):
             + 768 * 4 * 2)
 
 
-def traversal_roofline(prof_time, prof_count, peaks):
-    """bytes/ray = 32*boxes + 80*prims + 48, flops/ray = 20*boxes/... for the dominant kernel class."""
+def traversal_roofline(prof_time, prof_count, peaks, scene_name, small_scene):
+    """bytes/ray = 32*boxes + 80*prims + 48 for the dominant traversal kernel, divided by its CUDA-event
+    time -- plus what makes the figure readable: whether it is a bound at all (`bound_valid`), the rays that were
+    really traced next to the reference-accounted ones, and the issue-slot figure ncu says binds these kernels."""
     ms = prof_time["ms"]
     top = max(("nee", "extend"), key=lambda k: ms[k])
     pre = "nee" if top == "nee" else "ext"
-    rays, boxes, prims = prof_count[pre + "_rays"], prof_count[pre + "_boxes"], prof_count[pre + "_prims"]
     launches = max(1, prof_time["launches"][top])
-    bytes_total = 32.0 * boxes + 80.0 * prims + 48.0 * rays
-    flops_total = 20.0 * boxes + prims * (36.0 + 30.0) + 9.0 * rays
-    secs = ms[top] * 1e-3
-    achieved = bytes_total / secs / 1e9 if secs > 0 else 0.0
     peak = peaks["hbm_gbs"]
     share = ms[top] / max(1e-12, sum(ms.values()))
+    ncu = peaks.get("ncu", {}).get(scene_name, {})
 
     def one(kernel, pre):  # the same figures for either traversal kernel
         r, b, p = prof_count[pre + "_rays"], prof_count[pre + "_boxes"], prof_count[pre + "_prims"]
+        traced = prof_count["nee_traced"] if pre == "nee" else r  # every extension ray is traced
         t = ms[kernel] * 1e-3
-        by = 32.0 * b + 80.0 * p + 48.0 * r
-        return {"rays": r, "boxes_per_ray": round(b / max(1, r), 3), "prims_per_ray": round(p / max(1, r), 3),
-                "bytes_per_ray": round(by / max(1, r), 1), "grays_per_s": round(r / t / 1e9, 3) if t > 0 else 0.0,
-                "achieved": round(by / t / 1e9, 1) if t > 0 else 0.0, "frac": round(by / t / 1e9 / peak, 4) if t > 0 else 0.0}
+        by = 32.0 * b + 80.0 * p + 48.0 * traced  # 48 B of ray in / hit out only for queries that are traced
+        fl = 20.0 * b + p * (36.0 + 30.0) + 9.0 * traced
+        out = {"rays_reference_accounting": r, "rays_traced": traced,
+               "boxes_per_traced_ray": round(b / max(1, traced), 3), "prims_per_traced_ray": round(p / max(1, traced), 3),
+               "bytes_per_traced_ray": round(by / max(1, traced), 1),
+               "grays_traced_per_s": round(traced / t / 1e9, 3) if t > 0 else 0.0,
+               "grays_reference_per_s": round(r / t / 1e9, 3) if t > 0 else 0.0,
+               "algorithmic_gbs": round(by / t / 1e9, 1) if t > 0 else 0.0,
+               "frac_of_hbm": round(by / t / 1e9 / peak, 4) if t > 0 else 0.0,
+               "fp32_tflops": round(fl / t / 1e12, 3) if t > 0 else 0.0, "ms": round(ms[kernel], 4)}
+        n = ncu.get("k_" + kernel)
+        if n:  # from the committed ncu pass of this build (tools/capture_profiles.sh -> profiles/ncu_metrics.json)
+            out["ncu"] = n
+            out["useful_issue_frac"] = round(n["issue_active_pct"] / 100.0 * n["lanes_per_warp_inst"] / 32.0, 4)
+        return out
 
+    kernels = {"k_extend": one("extend", "ext"), "k_nee": one("nee", "nee")}
+    k = kernels["k_" + top]
+    frac = k["frac_of_hbm"]
+    valid = (not small_scene) and frac <= 1.2
+    why = ("scene records are staged in shared memory: the 8d byte count never comes from HBM" if small_scene else
+           ("frac > 1.2: served from L1/L2, not HBM" if frac > 1.2 else
+            "scene is L2-resident (1.6 MB): an upper bound on fetch traffic, not on DRAM traffic"))
     return {
-        "traversal_kernels": {"k_extend": one("extend", "ext"), "k_nee": one("nee", "nee")},
-        "bound": "hbm", "kernel": "k_nee" if top == "nee" else "k_extend", "achieved": achieved, "peak": peak,
-        "unit": "GB/s", "frac": achieved / peak, "peak_source": peaks["source"], "traffic": peaks.get("traffic"),
-        "algorithmic_bytes_per_launch": bytes_total / launches, "avg_launch_ms": ms[top] / launches,
-        "launches": launches, "rays": rays, "boxes_per_ray": boxes / max(1, rays), "prims_per_ray": prims / max(1, rays),
-        "bytes_per_ray": bytes_total / max(1, rays), "grays_per_s": rays / secs / 1e9 if secs > 0 else 0.0,
-        "fp32_tflops": flops_total / secs / 1e12 if secs > 0 else 0.0,
-        "fp32_frac_of_nominal": (flops_total / secs / 1e12) / FP32_PEAK_TFLOPS if secs > 0 else 0.0,
-        "share_of_step": share, "kernel_ms": {k: round(v, 4) for k, v in ms.items()},
-        "note": "scene data (BVH + instance table) is L2-resident; the byte figure is the algorithmic node/primitive "
-                "fetch traffic of SURVEY.md 8d, not DRAM traffic",
+        "bound": "hbm", "kernel": "k_" + top, "achieved": k["algorithmic_gbs"], "peak": peak, "unit": "GB/s",
+        "frac": frac, "bound_valid": valid, "bound_note": why, "peak_source": peaks["source"],
+        "traffic": (k.get("ncu") or {}).get("dram_bytes_per_launch"),
+        "traffic_source": (peaks.get("ncu_source") if k.get("ncu") else None),
+        "algorithmic_bytes_per_launch": k["algorithmic_gbs"] * 1e9 * ms[top] * 1e-3 / launches,
+        "avg_launch_ms": ms[top] / launches, "launches": launches, "share_of_step": share,
+        "issue_bound": {"what": "smsp__issue_active x (active lanes / 32) of the same kernel: the fraction of the SM's "
+                                "issue slots doing useful lane work -- the resource ncu shows these kernels are bound by",
+                        "frac": k.get("useful_issue_frac")},
+        "fp32_frac_of_nominal": k["fp32_tflops"] / FP32_PEAK_TFLOPS,
+        "traversal_kernels": kernels, "kernel_ms": {kk: round(v, 4) for kk, v in ms.items()},
     }
 
 
@@ -226,11 +260,22 @@ def load_peaks():
         with open(path) as f:
             j = json.load(f)
         peaks = {"hbm_gbs": float(j["hbm_gbs"]), "source": "measured (MEASURED_PEAKS.json, burst copy)"}
-    tr = os.path.join(ROOT, "profiles", "traffic.json")  # dram bytes per launch of the top kernel from ncu --set full
-    if os.path.exists(tr):
-        with open(tr) as f:
-            peaks["traffic"] = json.load(f).get("dram_bytes_per_launch")
+    nc = os.path.join(ROOT, "profiles", "ncu_metrics.json")  # ncu --set full figures of the top kernels, per scene
+    if os.path.exists(nc):
+        with open(nc) as f:
+            j = json.load(f)
+        peaks["ncu"] = j.get("scenes", {})
+        peaks["ncu_source"] = f"profiles/ncu_metrics.json (ncu --set full, commit {j.get('commit', '?')})"
     return peaks
+
+
+def pick_batch(count, auto):
+    """Samples per wavefront batch: the largest divisor of a rank's per-step share that fits the automatic batch."""
+    best = 1
+    for d in range(1, count + 1):
+        if count % d == 0 and d <= auto:
+            best = d
+    return best
 
 
 def ours_arm(args):
@@ -260,28 +305,25 @@ def ours_arm(args):
     cfgd = config_dict(args)
     w, h = cfgd["film"]["width"], cfgd["film"]["height"]
     npix = w * h
-    spp_step = args.spp_per_step or (4 if npix > 4_000_000 else 16)
+    spp_step = args.spp_per_step or (256 if 1_000_000 <= npix < 2_000_000 else 64)  # TOTAL over all ranks
+    if spp_step < world:
+        raise SystemExit("bench.py: --spp-per-step must be at least the number of GPUs")
     K, W = args.steps, max(args.warmup, 3)
     with open(cfgd["scene"]) as f:
         scene_json = f.read()
     cfg_json = json.dumps(cfgd)
 
     # ---- device-timed region: inputs (scene, wavefront state) resident in HBM ----------------------------------------
+    # STRONG scaling: the job is (W + K) x spp_step samples of every pixel whatever the number of GPUs; rank r renders the
+    # contiguous share shard_samples() gives it (global Philox sample indices), count_r spp of it per step.
     scene = pt.Scene.from_json(scene_json, w, h, device=local)
-    total_spp = (W + K) * spp_step
+    first_r, count_r = ptd.shard_samples(spp_step, world, rank)
     base = pt.Config.from_json(cfg_json).replace(device=local)
-    # rank r renders global samples [r * total_spp, (r+1) * total_spp): weak scaling, disjoint Philox streams
-    cfg = base.replace(samples=total_spp, sample_offset=rank * total_spp, batch_samples=0)
-    r = pt.renderer_from_config(scene, cfg).start_render()
     target_slots = int(os.environ.get("B200PT_BATCH_SLOTS", "0")) or (32 << 20)
-    batch = max(1, min(target_slots // npix, total_spp))  # the library's automatic wavefront batch (capi.cu)
-    batches_per_step = -(-spp_step // batch)
-    assert spp_step % batch == 0 or batch > spp_step, "a step must be a whole number of wavefront batches"
-    if batch > spp_step:
-        r.close()
-        cfg = cfg.replace(batch_samples=spp_step)
-        r = pt.renderer_from_config(scene, cfg).start_render()
-        batches_per_step = 1
+    batch = pick_batch(count_r, max(1, target_slots // npix))
+    batches_per_step = count_r // batch
+    cfg = base.replace(samples=(W + K) * count_r, sample_offset=(W + K) * first_r, batch_samples=batch)
+    r = pt.renderer_from_config(scene, cfg).start_render()
     for _ in range(W):
         r.sync_progress(batches_per_step)
     film = ptd.film_tensor(r)
@@ -292,13 +334,15 @@ def ours_arm(args):
         del scratch
     launches0 = sum(r.profile()["launches"].values())
     p0 = r.progress
-    t_dev0, paths0, rays0 = p0.seconds, p0.samples_done, p0.rays_extension + p0.rays_shadow
+    t_dev0, paths0 = p0.seconds, p0.samples_done
+    rays0 = (p0.rays_extension, p0.rays_shadow)
     red0, red1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     with ClockSampler(local) as clocks:
         wall0 = time.perf_counter()
         for _ in range(K):
             r.sync_progress(batches_per_step)  # device time by CUDA events on the render stream (capi.cu poll)
+        local_ck = film.double().sum(dim=(0, 1)) if world > 1 else None  # per-channel checksum of this rank's film
         red0.record()
         if world > 1:
             ptd.reduce_film(film, 0)  # the one exchange step: NCCL sum-reduce of the film to rank 0
@@ -308,22 +352,32 @@ def ours_arm(args):
     p1 = r.progress
     dev_s = (p1.seconds - t_dev0) + red0.elapsed_time(red1) * 1e-3
     paths = p1.samples_done - paths0
-    rays = p1.rays_extension + p1.rays_shadow - rays0
+    rays_ext, rays_shadow = p1.rays_extension - rays0[0], p1.rays_shadow - rays0[1]
     launches = sum(r.profile()["launches"].values()) - launches0 + (1 if world > 1 else 0)
+    film_check = None
+    if world > 1:
+        # a checksum of checksums: the reduced film on rank 0 must sum to the sum of the per-rank sums, channel by
+        # channel, and its unused .w lane must still be zero (a wrong root, a stale stream or garbage lanes show here)
+        dist.all_reduce(local_ck, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            got = film.double().sum(dim=(0, 1))
+            rel = ((got[:3] - local_ck[:3]).abs() / local_ck[:3].abs().clamp_min(1e-30)).max().item()
+            film_check = {"what": "per-channel sum of the NCCL-reduced film vs the sum of the per-rank film sums (float64)",
+                          "checksum_rel_err": rel, "w_lane_abs_sum": float(got[3].abs().item()),
+                          "ok": bool(rel < 1e-5 and got[3].abs().item() == 0.0)}
     stat = torch.tensor([dev_s, wall], dtype=torch.float64, device="cuda")
-    cnt = torch.tensor([paths, rays, launches], dtype=torch.int64, device="cuda")
+    cnt = torch.tensor([paths, rays_ext, rays_shadow, launches], dtype=torch.int64, device="cuda")
     if world > 1:
         dist.all_reduce(stat, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
     dev_s, wall = [float(x) for x in stat.tolist()]
-    paths, rays, launches = [int(x) for x in cnt.tolist()]
+    paths, rays_ext, rays_shadow, launches = [int(x) for x in cnt.tolist()]
     r.close()
 
     # ---- end to end through the public API: host JSON in, film in host memory out, every step ----------------------
     def e2e_step(step):
         sc = pt.Scene.from_json(scene_json, w, h, device=local)                     # parse + BVH + H2D upload
-        c = pt.Config.from_json(cfg_json).replace(device=local, samples=spp_step * world,
-                                                  sample_offset=step * spp_step * world)
+        c = pt.Config.from_json(cfg_json).replace(device=local, samples=spp_step, sample_offset=step * spp_step)
         rr, rep = ptd.render_sharded(sc, c, rank, world)                            # render (+ NCCL reduce)
         fb = rr.framebuffer if rank == 0 else None                                  # D2H read of the film
         rr.close()
@@ -334,8 +388,8 @@ def ours_arm(args):
     barrier()
     e0 = time.perf_counter()
     e_paths = 0
-    for s in range(K):
-        rep, fb = e2e_step(s + 1)
+    for s_ in range(K):
+        rep, fb = e2e_step(s_ + 1)
         e_paths += rep["camera_rays"] if rank == 0 else 0
     barrier()
     e_wall = torch.tensor([time.perf_counter() - e0], dtype=torch.float64, device="cuda")
@@ -343,10 +397,11 @@ def ours_arm(args):
         dist.all_reduce(e_wall, op=dist.ReduceOp.MAX)
     e_wall = float(e_wall.item())
     h2d = scene_upload_bytes(scene)
-    d2h = npix * 16
-    return dict(rank=rank, world=world, local=local, cfgd=cfgd, w=w, h=h, spp_step=spp_step, K=K, W=W, dev_s=dev_s,
-                wall=wall, paths=paths, rays=rays, launches=launches, clocks=clocks.summary(), e_wall=e_wall,
-                e_paths=e_paths, h2d=h2d, d2h=d2h, scene=scene, base=base, batch=min(batch, spp_step))
+    d2h = npix * 12
+    return dict(rank=rank, world=world, local=local, cfgd=cfgd, w=w, h=h, spp_step=spp_step, spp_rank=count_r, K=K, W=W,
+                dev_s=dev_s, wall=wall, paths=paths, rays_ext=rays_ext, rays_shadow=rays_shadow, launches=launches,
+                clocks=clocks.summary(), e_wall=e_wall, e_paths=e_paths, h2d=h2d, d2h=d2h, scene=scene, base=base,
+                batch=batch, film_check=film_check, small_scene=scene.desc().n_instances <= 16)
 
 
 def profile_passes(res):
@@ -355,7 +410,7 @@ def profile_passes(res):
     import pathtrace_b200 as pt
     out = []
     for mode in (1, 2):
-        cfg = res["base"].replace(samples=res["spp_step"], sample_offset=0, batch_samples=res["batch"], profile=mode)
+        cfg = res["base"].replace(samples=res["spp_rank"], sample_offset=0, batch_samples=res["batch"], profile=mode)
         r = pt.renderer_from_config(res["scene"], cfg).start_render()
         if mode == 1:  # warm the caches / clocks like the timed region
             warm = pt.renderer_from_config(res["scene"], cfg.replace(profile=0)).start_render()
@@ -380,35 +435,54 @@ def main():
             dist.destroy_process_group()
         return 0
     prof_time, prof_count = profile_passes(res)
-    roof = traversal_roofline(prof_time, prof_count, load_peaks())
+    roof = traversal_roofline(prof_time, prof_count, load_peaks(), args.scene, res["small_scene"])
     cpu = None
     if world == 1 and not args.no_cpu_baseline and os.path.exists(REF_DRIVER):
         threads = os.cpu_count() or 1
         try:
-            spp, _ = cpu_sample_spp(res["cfgd"], threads, args.cpu_seconds)
-            run = run_reference_once(res["cfgd"], spp, threads)
+            spp, run = cpu_sample(res["cfgd"], threads, args.cpu_seconds)
             cpu = {"value": run["mpaths_per_s"], "unit": "Mpaths/s", "cores": threads, "kind": "reference",
                    "mrays_per_s": run["mrays_per_s"], "seconds": run["seconds"],
                    "sample": f"{args.scene} {res['w']}x{res['h']} at {spp} spp, unmodified reference main() "
                              f"(tiled, 32x32 blocks, {threads} threads)"}
+            if args.cpu_one_thread:  # the deterministic single-thread rate (no RNG race), on a reduced film
+                one = dict(res["cfgd"], film=dict(res["cfgd"]["film"], width=max(32, res["w"] // 8),
+                                                  height=max(18, res["h"] // 8)))
+                r1 = run_reference_once(one, 1, 1)
+                cpu["one_thread"] = {"value": r1["mpaths_per_s"], "mrays_per_s": r1["mrays_per_s"],
+                                     "sample": f"{one['film']['width']}x{one['film']['height']} at 1 spp, 1 thread"}
         except Exception as e:  # the baseline is reported, never required
             cpu = {"value": None, "unit": "Mpaths/s", "cores": threads, "kind": "reference", "sample": f"failed: {e}"}
     value = res["paths"] / res["dev_s"] * 1e-6
+    rays = res["rays_ext"] + res["rays_shadow"]
+    # shadow queries really traced = reference-accounted ones x the traced share measured by the counters-on pass
+    nee = roof["traversal_kernels"]["k_nee"]
+    traced_share = nee["rays_traced"] / max(1, nee["rays_reference_accounting"])
+    rays_traced = res["rays_ext"] + res["rays_shadow"] * traced_share
     line = {
         "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": res["K"],
-        "warmup": res["W"], "ms_per_step": res["dev_s"] / res["K"] * 1e3, "higher_is_better": True, "scaling": "weak",
+        "warmup": res["W"], "ms_per_step": res["dev_s"] / res["K"] * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.scene} {res['w']}x{res['h']}, iterative nee path tracing, max_bounces 10, "
-                               f"light_samples 4, RR on (BASELINE configs: cornell_box = configs[1])",
-                   "spp_per_step_per_gpu": res["spp_step"], "wavefront_batch_spp": res["batch"],
-                   "parallelism": f"spp-sharding x{world}, one NCCL reduce of the film",
+        "config": {"workload": workload_name(args, res["w"], res["h"]),
+                   "spp_per_step_total": res["spp_step"], "spp_per_step_this_rank": res["spp_rank"],
+                   "wavefront_batch_spp": res["batch"],
+                   "parallelism": f"spp-sharding x{world} (strong: the step's samples are split over the ranks), one NCCL "
+                                  f"reduce of the film closes the job",
                    "l2": "per-step wavefront state (>= 1.3 GB) exceeds the 126 MB L2; no flush needed"},
-        "mrays_per_s": res["rays"] / res["dev_s"] * 1e-6, "rays_per_path": res["rays"] / max(1, res["paths"]),
+        "mrays_per_s": rays / res["dev_s"] * 1e-6, "rays_per_path": rays / max(1, res["paths"]),
+        "rays": {"rule": "Mrays/s counts what the reference counts (integrator.h:192,247): one per path segment + "
+                         "light_samples per vertex, including light samples that need no ray (coefficient 0: light below the "
+                         "horizon, pdf 0). mrays_traced_per_s counts only queries that are really intersected.",
+                 "extension": res["rays_ext"], "shadow_reference_accounting": res["rays_shadow"],
+                 "shadow_traced_share": round(traced_share, 4),
+                 "mrays_traced_per_s": rays_traced / res["dev_s"] * 1e-6},
         "wall_ms_per_step": res["wall"] / res["K"] * 1e3,
         "e2e": {"value": res["e_paths"] / res["e_wall"] * 1e-6, "unit": "Mpaths/s",
                 "h2d_bytes_per_step": res["h2d"], "d2h_bytes_per_step": res["d2h"],
-                "what": "per step: scene JSON (host) -> b200pt_scene_create_from_json -> render -> film read to host"},
+                "what": "per step: scene JSON (host) -> b200pt_scene_create_from_json -> render (sharded) -> NCCL reduce -> "
+                        "film read to host"},
         "gpu_launches": res["launches"], "clocks": res["clocks"], "roofline": roof, "cpu_baseline": cpu,
+        "film_check": res["film_check"],
     }
     print(json.dumps(line), flush=True)
     if world > 1:

@@ -286,6 +286,10 @@ typedef struct b200pt_profile {
     /* profile == 2: traversal work of the extension rays (k_extend) and of the shadow rays (k_nee) */
     uint64_t ext_rays, ext_boxes, ext_prims;
     uint64_t nee_rays, nee_boxes, nee_prims;
+    /* profile == 2: shadow queries that were really traced.  nee_rays follows the reference's accounting
+     * (integrator.h:247: light_samples per vertex) and includes the samples whose coefficient is zero -- light below
+     * the horizon, pdf 0 -- for which nothing is intersected. */
+    uint64_t nee_traced;
 } b200pt_profile;
 int b200pt_render_profile(b200pt_render *render, b200pt_profile *out);
 

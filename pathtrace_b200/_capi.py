@@ -76,7 +76,8 @@ class Progress(C.Structure):
 class Profile(C.Structure):
     _fields_ = [("ms", C.c_double * 5), ("launches", C.c_int64 * 5),
                 ("ext_rays", C.c_uint64), ("ext_boxes", C.c_uint64), ("ext_prims", C.c_uint64),
-                ("nee_rays", C.c_uint64), ("nee_boxes", C.c_uint64), ("nee_prims", C.c_uint64)]
+                ("nee_rays", C.c_uint64), ("nee_boxes", C.c_uint64), ("nee_prims", C.c_uint64),
+                ("nee_traced", C.c_uint64)]
 
 
 KERNEL_NAMES = ("raygen", "extend", "shade", "nee", "accumulate")

@@ -814,7 +814,7 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         r->n_rows = c.max_bounces + 3;
         wf.counters = render_alloc<int32_t>(*r, (size_t)pt::CNT_ROW * r->n_rows, true);
         wf.ctl = render_alloc<pt::BatchCtl>(*r, 1, true);
-        wf.trace_counts = render_alloc<unsigned long long>(*r, 6, true);
+        wf.trace_counts = render_alloc<unsigned long long>(*r, 8, true);
         pt::BatchCtl ctl{};
         ctl.sample_base = c.sample_offset;
         ctl.nsamp = bs;
@@ -1158,12 +1158,13 @@ int b200pt_render_profile(b200pt_render *r, b200pt_profile *out)
         return fail(B200PT_ERR_INVALID, "null argument");
     return guarded([&] {
         need_device(r->scene);
-        unsigned long long h[6];
+        unsigned long long h[8];
         CK(cudaMemcpyAsync(h, r->wf.trace_counts, sizeof(h), cudaMemcpyDeviceToHost, r->scene->stream));
         CK(cudaStreamSynchronize(r->scene->stream));
         *out = r->prof;
         out->ext_rays = h[0], out->ext_boxes = h[1], out->ext_prims = h[2];
         out->nee_rays = h[3], out->nee_boxes = h[4], out->nee_prims = h[5];
+        out->nee_traced = h[6];
     });
 }
 

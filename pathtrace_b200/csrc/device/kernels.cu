@@ -87,18 +87,22 @@ struct SmallScene {
 };
 
 // work counters of one thread -> global totals (profile == 2 only)
-__device__ __forceinline__ void flush_counts(const TraceCounters &tc, unsigned long long rays, unsigned long long *dst)
+__device__ __forceinline__ void flush_counts(const TraceCounters &tc, unsigned long long rays, unsigned long long *dst,
+                                             unsigned long long traced = 0, unsigned long long *dst_traced = nullptr)
 {
-    unsigned long long b = tc.boxes, p = tc.prims, r = rays;
+    unsigned long long b = tc.boxes, p = tc.prims, r = rays, t = traced;
     for (int off = 16; off > 0; off >>= 1) {
         b += __shfl_down_sync(0xffffffffu, b, off);
         p += __shfl_down_sync(0xffffffffu, p, off);
         r += __shfl_down_sync(0xffffffffu, r, off);
+        t += __shfl_down_sync(0xffffffffu, t, off);
     }
     if ((threadIdx.x & 31) == 0) {
         atomicAdd(dst + 0, r);
         atomicAdd(dst + 1, b);
         atomicAdd(dst + 2, p);
+        if (dst_traced)
+            atomicAdd(dst_traced, t);
     }
 }
 
@@ -342,7 +346,7 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
         s_small.stage(s);
     TraceCounters tc;
     tc.boxes = tc.prims = 0;
-    unsigned long long nrays = 0;
+    unsigned long long nrays = 0, ntraced = 0;
     const long long sample_base = wf.ctl->sample_base;
     const int L = rp.light_samples;
     // The samples of one vertex occupy a group of P adjacent lanes, P = light_samples rounded up to a power of two
@@ -386,6 +390,8 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
             mr = nee_medium_rng(key, bounce, k);
             T.init(xyz(hp), ns.dir, 0.001f, PT_FLT_MAX);
             trace = !nee_is_void(ns);
+            if (COUNT && trace)
+                ntraced++; // a query that really is traced (void samples are counted as rays, never walked)
             if (ANY && trace) {
                 trace = T.template emitters_first<COUNT>(s, &tc, ns.known_inst, &ns.known);
                 lit = T.best_inst;
@@ -439,7 +445,7 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
         }
     }
     if (COUNT)
-        flush_counts(tc, nrays, wf.trace_counts + 3);
+        flush_counts(tc, nrays, wf.trace_counts + 3, ntraced, wf.trace_counts + 6);
 }
 
 // framebuffer[j][i] += de_nan(col): one thread per pixel walks the samples of the batch in order, so the film is

@@ -51,7 +51,7 @@ struct Wavefront {
     int32_t *path_count;
     int32_t path_max, path_stride;
     float path_prob;
-    unsigned long long *trace_counts; // profile == 2: {ext rays, boxes, prims, nee rays, boxes, prims}
+    unsigned long long *trace_counts; // profile == 2: {ext rays, boxes, prims, nee rays, boxes, prims, nee rays traced, -}
     int32_t npix;
     int32_t capacity; // slots
     uint32_t npix_mul, npix_shr; // slot / npix == umulhi(slot, npix_mul) >> npix_shr (npix_mul == 0: npix == 1)

@@ -62,9 +62,9 @@ def render_sharded(scene, config, rank=0, world_size=1, group=None):
     the final image), on other ranks their own share."""
     import torch
     from .renderer import renderer_from_config
-    first, count = shard_samples(config.samples, world_size, rank)
-    if count == 0:
+    if config.samples < world_size:  # checked before sharding, so that EVERY rank raises (none is left in the reduce)
         raise ValueError("fewer samples than ranks: use fewer GPUs")
+    first, count = shard_samples(config.samples, world_size, rank)
     cfg = config.replace(samples=count, sample_offset=config.sample_offset + first)
     r = renderer_from_config(scene, cfg).start_render()
     report = r.finalize()

@@ -209,6 +209,9 @@ class Wavefront:
         self.config = config
         self._h = None
         self.progress = _capi.Progress()
+        # samples per pixel the film's sums stand for: config.samples, or -- on rank 0 after a sharded render has
+        # reduced every rank's share into this film (distributed.render_sharded) -- the samples of ALL ranks
+        self.spp_total = config.samples
 
     # -- lifecycle ---------------------------------------------------------------------------------------------
     def preprocess(self):
@@ -277,7 +280,7 @@ class Wavefront:
         p = _capi.Profile()
         check(lib().b200pt_render_profile(self._h, C.byref(p)))
         out = {"ms": dict(zip(_capi.KERNEL_NAMES, p.ms[:])), "launches": dict(zip(_capi.KERNEL_NAMES, p.launches[:]))}
-        for k in ("ext_rays", "ext_boxes", "ext_prims", "nee_rays", "nee_boxes", "nee_prims"):
+        for k in ("ext_rays", "ext_boxes", "ext_prims", "nee_rays", "nee_boxes", "nee_prims", "nee_traced"):
             out[k] = getattr(p, k)
         return out
 
@@ -293,7 +296,7 @@ class Wavefront:
 
     def tonemap(self, n_samples=None):
         """(H, W, 3) uint8 image, TOP row first, plus (max_luminance, avg_luminance)."""
-        n = n_samples if n_samples is not None else self.config.samples
+        n = n_samples if n_samples is not None else self.spp_total
         h, w = self.config.height, self.config.width
         out = np.zeros((h, w, 3), dtype=np.uint8)
         mx, avg = C.c_float(), C.c_float()
@@ -301,7 +304,7 @@ class Wavefront:
         return out, mx.value, avg.value
 
     def write_ppm(self, path, n_samples=None):
-        n = n_samples if n_samples is not None else self.config.samples
+        n = n_samples if n_samples is not None else self.spp_total
         d = os.path.dirname(path)
         if d:
             os.makedirs(d, exist_ok=True)  # the reference needs pre_render.py for this

@@ -9,7 +9,7 @@ Inputs are per-pixel statistics of the radiance samples of one film (H x W x 3, 
   ours       csum / csq over n_ours clamped samples and the unclamped sums (+ optionally unclamped squares)
 
 Steps (numbering of SURVEY 8c):
-  (2) per-pixel z-scores on clamped samples: mean |z| small, <= 2 % beyond 3, none beyond 6
+  (2) per-pixel z-scores on clamped samples at EQUAL sample counts: |mean z| < 0.15, < 1 % beyond 3, < 0.1 % beyond 6
   (3) rRMSE of 8x8-block means, ours-vs-reference, next to the reference-vs-replica floor: pass <= 1.2 x floor.
       Evaluated on the clamped means (finite variance -- the reference estimator's unclamped variance is infinite, Q4)
       and REPORTED on the unclamped means
@@ -54,17 +54,28 @@ def rrmse(a, b):
     return float(np.sqrt(np.mean((a - b) ** 2)) / max(1e-30, float(np.mean(b))))
 
 
-def evaluate(g, csum, csq, n_ours, sums, sq_unclamped=None, block=8):
-    """Returns the report dict; raises AssertionError naming the step that failed."""
+def evaluate(g, first, total, sq_unclamped=None, block=8):
+    """first = (csum, csq, n) of ours over exactly the reference's sample count; total = (csum, csq, sums, n) over all
+    our samples (n >= 2 x the reference's).  Returns the report dict; raises AssertionError naming the step that failed.
+
+    Step 2 compares EQUAL sample counts: the samples are heavily right-skewed (small lights, Q4), a pixel mean over
+    1024 of them is more often below than above its expectation and its variance estimate moves with it, so z-scores of
+    a 4096-sample mean against a 1024-sample reference come out shifted (measured: mean z 0.37 on
+    cornell_box_small_lights, identically for the GPU and the CPU restatement) although both draw from one
+    distribution; between two 1024-sample estimates the effect cancels (reference vs its replica: mean z 0.01-0.03)."""
     n_ref = g["n"]
-    mean_c = csum.astype(np.float64) / n_ours
-    var_c = np.maximum(csq.astype(np.float64) / n_ours - mean_c ** 2, 0) * n_ours / (n_ours - 1)
+    csum1, csq1, n1 = first
+    assert n1 == n_ref, (n1, n_ref)
+    mean1 = csum1.astype(np.float64) / n1
+    var1 = np.maximum(csq1.astype(np.float64) / n1 - mean1 ** 2, 0) * n1 / (n1 - 1)
     var_r = g["cm2"] / (n_ref - 1)
-    se = np.sqrt(var_c / n_ours + var_r / n_ref)
+    se = np.sqrt(var1 / n1 + var_r / n_ref)
     ok = se > 0
-    z = (mean_c[ok] - g["cmean"][ok]) / se[ok]
+    z = (mean1[ok] - g["cmean"][ok]) / se[ok]
+    csum, csq, sums, n_ours = total
     rep = {"n_ours": int(n_ours), "n_ref": int(n_ref), "z_mean": float(z.mean()), "z_abs_mean": float(np.abs(z).mean()),
            "z_gt3": float((np.abs(z) > 3).mean()), "z_gt6": float((np.abs(z) > 6).mean()), "z_max": float(np.abs(z).max())}
+    mean_c = csum.astype(np.float64) / n_ours
     mean_u = sums.astype(np.float64) / n_ours
     rep["global_mean_ours"] = float(mean_u.mean())
     rep["global_mean_ref"] = float(g["mean"].mean())
@@ -83,11 +94,12 @@ def evaluate(g, csum, csq, n_ours, sums, sq_unclamped=None, block=8):
         rep["global_mean_sigma"] = sigma
         rep["global_mean_dev_sigmas"] = abs(rep["global_mean_ours"] - rep["global_mean_ref"]) / max(sigma, 1e-30)
     # ---- the gates ----
-    assert abs(rep["z_mean"]) < 0.2, ("step 2: mean z", rep)  # skewed samples bias z by O(skew / sqrt(n))
-    assert rep["z_gt3"] < 0.02, ("step 2: |z| > 3", rep)
+    assert abs(rep["z_mean"]) < 0.15, ("step 2: mean z", rep)
+    assert rep["z_gt3"] < 0.01, ("step 2: |z| > 3", rep)
     assert rep["z_gt6"] < 1e-3, ("step 2: |z| > 6", rep)
-    np.testing.assert_allclose(mean_c[~ok], g["cmean"][~ok], rtol=1e-4, atol=1e-6)  # deterministic pixels
+    np.testing.assert_allclose(mean1[~ok], g["cmean"][~ok], rtol=1e-4, atol=1e-6)  # deterministic pixels
     if "rep_mean" in g:
+        assert n_ours >= 2 * n_ref
         assert rep["block_rrmse_clamped"] <= 1.2 * rep["block_rrmse_clamped_floor"], ("step 3: block rRMSE", rep)
     if sq_unclamped is not None:
         assert rep["global_mean_dev_sigmas"] < 3.0, ("step 4: unclamped global mean", rep)

@@ -101,15 +101,19 @@ def test_full_depth_protocol_restatement_vs_reference(tag):
     g = parity_protocol.load_golden(tag)
     cfgd = dict(g["config"])
     cfgd["scene"] = scene_path(os.path.basename(cfgd["scene"]).replace(".json", ""))
-    n = 2048  # twice the reference's count: ours-vs-reference is then expected at ~0.87 x the same-count floor, and the
-    cfgd["samples"] = n  # 1.2 x gate is three standard deviations of the RMSE estimate away (64 blocks)
+    n1 = g["n"]  # step 2 at the reference's own sample count, steps 3-4 over twice as many (parity_protocol.evaluate)
+    n = 2 * n1
     w, h = cfgd["film"]["width"], cfgd["film"]["height"]
     oracle = PortOracle.from_file(cfgd["scene"], w, h)
-    out = oracle.render(make_cconfig(cfgd, stats_clamp=g["clamp"], seed=4242))
+    cfgd["samples"] = n1
+    a = oracle.render(make_cconfig(cfgd, stats_clamp=g["clamp"], seed=4242))
+    b = oracle.render(make_cconfig(cfgd, stats_clamp=g["clamp"], seed=4242, sample_offset=n1))
+    out = {k: a[k] + b[k] for k in ("csum", "csq", "sums", "rays_reference")}
     sq = None
     if tag == "cornell_box_full":  # step 4 needs the unclamped second moment: a second pass with the clamp out of reach
+        cfgd["samples"] = n
         sq = oracle.render(make_cconfig(cfgd, stats_clamp=1e30, seed=4242))["csq"]
-    rep = parity_protocol.evaluate(g, out["csum"], out["csq"], n, out["sums"], sq)
+    rep = parity_protocol.evaluate(g, (a["csum"], a["csq"], n1), (out["csum"], out["csq"], out["sums"], n), sq)
     ref_rays_per_path = float(g["total_rays"]) / (w * h * g["n"])
     got = out["rays_reference"] / (w * h * n)
     assert abs(got - ref_rays_per_path) < 0.03 * ref_rays_per_path, (got, ref_rays_per_path)
