@@ -218,6 +218,7 @@ def traversal_roofline(prof_time, prof_count, peaks, scene_name, small_scene):
         by = 32.0 * b + 80.0 * p + 48.0 * traced  # 48 B of ray in / hit out only for queries that are traced
         fl = 20.0 * b + p * (36.0 + 30.0) + 9.0 * traced
         out = {"rays_reference_accounting": r, "rays_traced": traced,
+               "rays_queued": prof_count["nee_queued"] if pre == "nee" else r,
                "boxes_per_traced_ray": round(b / max(1, traced), 3), "prims_per_traced_ray": round(p / max(1, traced), 3),
                "bytes_per_traced_ray": round(by / max(1, traced), 1),
                "grays_traced_per_s": round(traced / t / 1e9, 3) if t > 0 else 0.0,

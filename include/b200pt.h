@@ -279,7 +279,8 @@ int b200pt_config_string(const char *config_json, const char *key, char *out, si
 #define B200PT_K_SHADE 2
 #define B200PT_K_NEE 3
 #define B200PT_K_ACCUMULATE 4
-#define B200PT_K_COUNT 5
+#define B200PT_K_SORT 5 /* coherence sort of the ray queues between bounces (BVH scenes) */
+#define B200PT_K_COUNT 6
 typedef struct b200pt_profile {
     double ms[B200PT_K_COUNT];        /* profile == 1: device time per kernel class, summed over launches */
     int64_t launches[B200PT_K_COUNT]; /* kernel launches per class so far (always counted) */
@@ -290,6 +291,8 @@ typedef struct b200pt_profile {
      * (integrator.h:247: light_samples per vertex) and includes the samples whose coefficient is zero -- light below
      * the horizon, pdf 0 -- for which nothing is intersected. */
     uint64_t nee_traced;
+    uint64_t nee_queued; /* light samples that occupied a lane of k_nee: nee_rays minus those of the vertices whose lights all
+                          * lie below their horizon (never queued) */
 } b200pt_profile;
 int b200pt_render_profile(b200pt_render *render, b200pt_profile *out);
 

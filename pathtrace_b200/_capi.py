@@ -74,13 +74,13 @@ class Progress(C.Structure):
 
 
 class Profile(C.Structure):
-    _fields_ = [("ms", C.c_double * 5), ("launches", C.c_int64 * 5),
+    _fields_ = [("ms", C.c_double * 6), ("launches", C.c_int64 * 6),
                 ("ext_rays", C.c_uint64), ("ext_boxes", C.c_uint64), ("ext_prims", C.c_uint64),
                 ("nee_rays", C.c_uint64), ("nee_boxes", C.c_uint64), ("nee_prims", C.c_uint64),
-                ("nee_traced", C.c_uint64)]
+                ("nee_traced", C.c_uint64), ("nee_queued", C.c_uint64)]
 
 
-KERNEL_NAMES = ("raygen", "extend", "shade", "nee", "accumulate")
+KERNEL_NAMES = ("raygen", "extend", "shade", "nee", "accumulate", "sort")
 
 HIT_DTYPE = np.dtype([("instance", "<i4"), ("t", "<f4"), ("p", "<f4", 3), ("n", "<f4", 3), ("u", "<f4"), ("v", "<f4")])
 assert HIT_DTYPE.itemsize == 40

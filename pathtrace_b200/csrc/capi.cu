@@ -455,6 +455,16 @@ void enqueue_batch(b200pt_render &r)
                 if (kinds & (1u << k))
                     pt::launch_shade(s, r.rp, r.wf, b, k, r.lc, st);
         });
+        if (r.wf.sort_on) {
+            const bool more = b + 1 < n_bounces;
+            launch_class(r, B200PT_K_SORT, (nee ? 3 : 0) + (more ? 3 : 0), [&] {
+                if (nee)
+                    pt::launch_sort_queue(r.wf, r.wf.key_nee, r.wf.q_raw_nee, r.wf.q_nee, b * pt::CNT_ROW + pt::CNT_NEE, r.lc, st);
+                if (more)
+                    pt::launch_sort_queue(r.wf, r.wf.key_ext, r.wf.q_raw_ext, r.wf.q_ext[(b + 1) & 1],
+                                          (b + 1) * pt::CNT_ROW + pt::CNT_EXT, r.lc, st);
+            });
+        }
         if (nee)
             launch_class(r, B200PT_K_NEE, 1, [&] { pt::launch_nee(s, r.rp, r.wf, b, r.lc, st); });
     }
@@ -798,19 +808,26 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
                 wf.npix_shr = l - 1;
             }
         }
-        wf.ray_o = render_alloc<float4>(*r, cap);
-        wf.ray_d = render_alloc<float4>(*r, cap);
-        wf.beta = render_alloc<float4>(*r, cap);
-        wf.att = render_alloc<float4>(*r, cap);
-        wf.hit_p = render_alloc<float4>(*r, cap);
-        wf.hit_n = render_alloc<float4>(*r, cap);
-        wf.nee_w = render_alloc<float4>(*r, cap);
-        wf.sum = render_alloc<float4>(*r, cap);
+        wf.ray = render_alloc<float4>(*r, 2 * cap);
+        wf.thr = render_alloc<float4>(*r, 2 * cap);
+        wf.hit = render_alloc<float4>(*r, 2 * cap);
+        wf.acc = render_alloc<float4>(*r, 2 * cap);
         for (int k = 0; k < 2; k++)
             wf.q_ext[k] = render_alloc<int32_t>(*r, cap);
         for (int k = 0; k < pt::SK_COUNT; k++)
             wf.q_kind[k] = render_alloc<int32_t>(*r, cap);
         wf.q_nee = render_alloc<int32_t>(*r, cap);
+        // coherence sort between bounces: scenes that walk the BVH (B200PT_SORT=0 switches it off, for A/B runs)
+        wf.sort_on = scene->view.n_small == 0 ? 1 : 0;
+        if (const char *e = std::getenv("B200PT_SORT"))
+            wf.sort_on = wf.sort_on && atoi(e) != 0;
+        if (wf.sort_on) {
+            wf.q_raw_ext = render_alloc<int32_t>(*r, cap);
+            wf.q_raw_nee = render_alloc<int32_t>(*r, cap);
+            wf.key_ext = render_alloc<uint32_t>(*r, cap);
+            wf.key_nee = render_alloc<uint32_t>(*r, cap);
+            wf.sort_hist = render_alloc<uint32_t>(*r, (size_t)PT_SORT_BUCKETS + PT_SORT_BUCKETS / PT_SORT_CHUNK);
+        }
         r->n_rows = c.max_bounces + 3;
         wf.counters = render_alloc<int32_t>(*r, (size_t)pt::CNT_ROW * r->n_rows, true);
         wf.ctl = render_alloc<pt::BatchCtl>(*r, 1, true);
@@ -1165,6 +1182,7 @@ int b200pt_render_profile(b200pt_render *r, b200pt_profile *out)
         out->ext_rays = h[0], out->ext_boxes = h[1], out->ext_prims = h[2];
         out->nee_rays = h[3], out->nee_boxes = h[4], out->nee_prims = h[5];
         out->nee_traced = h[6];
+        out->nee_queued = h[7];
     });
 }
 

@@ -101,8 +101,10 @@ __device__ __forceinline__ void flush_counts(const TraceCounters &tc, unsigned l
         atomicAdd(dst + 0, r);
         atomicAdd(dst + 1, b);
         atomicAdd(dst + 2, p);
-        if (dst_traced)
+        if (dst_traced) {
             atomicAdd(dst_traced, t);
+            atomicAdd(dst_traced + 1, r); // queries that occupied a lane (queued), as opposed to merely counted
+        }
     }
 }
 
@@ -129,6 +131,52 @@ __device__ __forceinline__ int shade_kind_of(int mat_kind)
     }
 }
 
+// ---- coherence sort keys ---------------------------------------------------------------------------------------------
+// 10 bits -> every third bit
+__device__ __forceinline__ uint32_t spread3(uint32_t x)
+{
+    x = (x | (x << 16)) & 0x030000FFu;
+    x = (x | (x << 8)) & 0x0300F00Fu;
+    x = (x | (x << 4)) & 0x030C30C3u;
+    x = (x | (x << 2)) & 0x09249249u;
+    return x;
+}
+
+// Morton code of the cell of p on a 2^bits grid over the scene's sort bounds (positions outside are clamped)
+template <int BITS> __device__ __forceinline__ uint32_t morton_cell(const PtSceneView &s, V3 p)
+{
+    const float top = (float)((1 << BITS) - 1), up = (float)(1 << BITS);
+    // fminf / fmaxf drop NaNs: a NaN coordinate lands in cell 0
+    const uint32_t cx = (uint32_t)fminf(fmaxf((p.x - s.sort_lo[0]) * (s.sort_scale[0] * up), 0.f), top);
+    const uint32_t cy = (uint32_t)fminf(fmaxf((p.y - s.sort_lo[1]) * (s.sort_scale[1] * up), 0.f), top);
+    const uint32_t cz = (uint32_t)fminf(fmaxf((p.z - s.sort_lo[2]) * (s.sort_scale[2] * up), 0.f), top);
+    return spread3(cx) | (spread3(cy) << 1) | (spread3(cz) << 2);
+}
+
+// next extension ray: direction bin (major) | cell of the origin -- rays of a warp start together and head the same way.
+// PT_SORT_DIR_BITS = 3: the octant of d; 2n > 3: an n x n-bit grid over the octahedral map of d
+__device__ __forceinline__ uint32_t sort_key_ext(const PtSceneView &s, V3 o, V3 d)
+{
+#if PT_SORT_DIR_BITS == 3
+    const uint32_t dir = (d.x < 0.f ? 1u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 4u : 0u);
+#else
+    constexpr int H = PT_SORT_DIR_BITS / 2;
+    const float inv = 1.0f / (fabsf(d.x) + fabsf(d.y) + fabsf(d.z));
+    float u = d.x * inv, v = d.y * inv;
+    if (d.z < 0.f) { // fold the lower half outwards
+        const float fu = (1.f - fabsf(v)) * (u < 0.f ? -1.f : 1.f), fv = (1.f - fabsf(u)) * (v < 0.f ? -1.f : 1.f);
+        u = fu, v = fv;
+    }
+    const float top = (float)((1 << H) - 1), half = (float)(1 << (H - 1));
+    const uint32_t bu = (uint32_t)fminf(fmaxf((u + 1.f) * half, 0.f), top), bv = (uint32_t)fminf(fmaxf((v + 1.f) * half, 0.f), top);
+    const uint32_t dir = (bv << H) | bu;
+#endif
+    return (dir << (3 * PT_SORT_CELL_BITS)) | morton_cell<PT_SORT_CELL_BITS>(s, o);
+}
+
+// light samples: all of them aim at the few lights, so the vertex position alone orders them (one more bit per axis)
+__device__ __forceinline__ uint32_t sort_key_nee(const PtSceneView &s, V3 p) { return morton_cell<PT_SORT_CELL_BITS + 1>(s, p); }
+
 // ---------------------------------------------------------------------------------------------------------------
 
 __global__ void __launch_bounds__(kThreads) k_raygen(PtSceneView s, RenderParams rp, Wavefront wf)
@@ -145,11 +193,12 @@ __global__ void __launch_bounds__(kThreads) k_raygen(PtSceneView s, RenderParams
         float v = (float)(j + (double)r.y) / (float)rp.height;
         V3 o, d;
         camera_ray(s.cam, u, v, r.z, r.w, o, d);
-        wf.ray_o[slot] = f4(o, -1.f); // last_bsdf_pdf = -1 (integrator.h:183)
-        wf.ray_d[slot] = f4(d, 0.f);
-        wf.beta[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
-        wf.att[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
-        wf.sum[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+        wf.ray[2 * slot] = f4(o, -1.f); // last_bsdf_pdf = -1 (integrator.h:183)
+        wf.ray[2 * slot + 1] = f4(d, 0.f);
+        wf.thr[2 * slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+        wf.thr[2 * slot + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        wf.acc[2 * slot] = make_float4(0.f, 0.f, 0.f, 0.f); // whole 32-byte sectors: no read-modify-write in L2
+        wf.acc[2 * slot + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (wf.path_id) { // `random_double() < trace_probability` (renderer.h:652)
             int id = -1;
             if (rng4(key, stage_word(0, RNG_PATH_TRACE, 0), 0).x < wf.path_prob) {
@@ -201,7 +250,7 @@ __global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView
         mr.xi = -1.f;
         if (live) {
             slot = q_in ? q_in[i] : i;
-            float4 ro = wf.ray_o[slot], rd = wf.ray_d[slot];
+            float4 ro = wf.ray[2 * slot], rd = wf.ray[2 * slot + 1];
             mr.key = make_key(rp, wf, slot, sample_base);
             mr.stage = stage_word(bounce, RNG_EXT_MEDIUM, 0);
             T.init(xyz(ro), xyz(rd), 0.001f, PT_FLT_MAX);
@@ -217,8 +266,8 @@ __global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView
             Hit h;
             int kind = SK_MISS;
             if (T.template result<MEDIA>(s, h)) {
-                wf.hit_p[slot] = f4(h.p, __int_as_float(h.inst | (h.face << kFaceShift)));
-                wf.hit_n[slot] = f4(h.n, h.t);
+                wf.hit[2 * slot] = f4(h.p, __int_as_float(h.inst | (h.face << kFaceShift)));
+                wf.hit[2 * slot + 1] = f4(h.n, h.t);
                 kind = shade_kind_of(s.mats[meta_material(s.inst[h.inst].meta)].kind);
             }
             mask = 1u << kind;
@@ -242,29 +291,32 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
     int32_t *row = wf.counters + bounce * CNT_ROW;
     const int n = row[CNT_KIND0 + kind];
     const int32_t *q_in = wf.q_kind[kind];
-    int32_t *q_next = wf.q_ext[(bounce + 1) & 1];
+    const bool sorted = wf.sort_on != 0;
+    int32_t *q_next = sorted ? wf.q_raw_ext : wf.q_ext[(bounce + 1) & 1];
+    int32_t *q_nee_out = sorted ? wf.q_raw_nee : wf.q_nee;
     int32_t *const counter[2] = {row + CNT_NEE, row + CNT_ROW + CNT_EXT};
     for (int base = blockIdx.x * kThreads; base < n; base += gridDim.x * kThreads) {
         const int i = base + threadIdx.x;
         unsigned mask = 0;
         int slot = 0;
         bool nee_skipped = false;
+        uint32_t key_nee = 0, key_ext = 0;
         if (i < n) {
             slot = q_in[i];
-            float4 ro = wf.ray_o[slot], rd = wf.ray_d[slot], bt = wf.beta[slot];
+            float4 ro = wf.ray[2 * slot], rd = wf.ray[2 * slot + 1], bt = wf.thr[2 * slot];
             if (kind == SK_MISS) {
                 V3 add = shade_miss(s, xyz(rd), xyz(bt));
-                const float4 acc = wf.sum[slot];
-                wf.sum[slot] = make_float4(acc.x + add.x, acc.y + add.y, acc.z + add.z, 0.f);
+                const float4 acc = wf.acc[2 * slot + 1];
+                wf.acc[2 * slot + 1] = make_float4(acc.x + add.x, acc.y + add.y, acc.z + add.z, 0.f);
             } else {
-                float4 hp = wf.hit_p[slot], hn = wf.hit_n[slot];
+                float4 hp = wf.hit[2 * slot], hn = wf.hit[2 * slot + 1];
                 PathVertexIn in;
                 in.o = xyz(ro);
                 in.d = xyz(rd);
                 in.beta = xyz(bt);
                 in.last_bsdf_pdf = ro.w;
                 // only a light leaves `attenuation` as the previous vertex set it (material.h:187-191)
-                in.attenuation = kind == SK_LIGHT ? xyz(wf.att[slot]) : v3(0.f, 0.f, 0.f);
+                in.attenuation = kind == SK_LIGHT ? xyz(wf.thr[2 * slot + 1]) : v3(0.f, 0.f, 0.f);
                 Hit rec;
                 rec.inst = __float_as_int(hp.w) & ((1 << kFaceShift) - 1);
                 rec.face = __float_as_int(hp.w) >> kFaceShift;
@@ -291,8 +343,8 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
                 else
                     shade_hit_rpt<kind>(s, rp, in, rec, bounce, rnd, out);
                 if (out.add.x != 0.f || out.add.y != 0.f || out.add.z != 0.f) { // rare: the sum is read only then
-                    const float4 acc = wf.sum[slot];
-                    wf.sum[slot] = make_float4(acc.x + out.add.x, acc.y + out.add.y, acc.z + out.add.z, 0.f);
+                    const float4 acc = wf.acc[2 * slot + 1];
+                    wf.acc[2 * slot + 1] = make_float4(acc.x + out.add.x, acc.y + out.add.y, acc.z + out.add.z, 0.f);
                 }
                 if (out.want_nee) {
                     // all lights below the horizon of this vertex: its light samples are all void (pt_shade.h), they
@@ -300,15 +352,19 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
                     if (NEE && !CORR && lights_below_horizon(s, rec.p, rec.n)) {
                         nee_skipped = true;
                     } else {
-                        wf.nee_w[slot] = f4(out.W, __int_as_float(out.mat_kind));
+                        wf.acc[2 * slot] = f4(out.W, __int_as_float(out.mat_kind));
                         mask |= 1u;
+                        if (sorted)
+                            key_nee = sort_key_nee(s, rec.p);
                     }
                 }
                 if (out.cont) {
-                    wf.ray_o[slot] = f4(out.o, out.last_bsdf_pdf);
-                    wf.ray_d[slot] = f4(out.d, 0.f);
-                    wf.beta[slot] = f4(out.beta, 0.f);
-                    wf.att[slot] = f4(out.attenuation, 0.f);
+                    if (sorted)
+                        key_ext = sort_key_ext(s, out.o, out.d);
+                    wf.ray[2 * slot] = f4(out.o, out.last_bsdf_pdf);
+                    wf.ray[2 * slot + 1] = f4(out.d, 0.f);
+                    wf.thr[2 * slot] = f4(out.beta, 0.f);
+                    wf.thr[2 * slot + 1] = f4(out.attenuation, 0.f);
                     mask |= 2u;
                 }
             }
@@ -322,10 +378,16 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
         }
         int pos[2];
         block_reserve<2>(mask, counter, pos);
-        if (mask & 1u)
-            wf.q_nee[pos[0]] = slot;
-        if (mask & 2u)
+        if (mask & 1u) {
+            q_nee_out[pos[0]] = slot;
+            if (sorted)
+                wf.key_nee[pos[0]] = key_nee;
+        }
+        if (mask & 2u) {
             q_next[pos[1]] = slot;
+            if (sorted)
+                wf.key_ext[pos[1]] = key_ext;
+        }
     }
 }
 
@@ -380,7 +442,7 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
         }
         if (e < n && k < L) {
             slot = wf.q_nee[q];
-            float4 hp = wf.hit_p[slot], hn = wf.hit_n[slot], w = wf.nee_w[slot];
+            float4 hp = wf.hit[2 * slot], hn = wf.hit[2 * slot + 1], w = wf.acc[2 * slot];
             RngKey key = make_key(rp, wf, slot, sample_base);
             nrays++;
             if (CORR)
@@ -429,13 +491,13 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
             if (slot >= 0 && (threadIdx.x & (P - 1)) == 0 && (c.x != 0.f || c.y != 0.f || c.z != 0.f)) {
                 // one lane per vertex and kernel touches sum[slot]: a reduction without a return value is as
                 // deterministic as load-add-store and does not wait for the load
-                float *dst = reinterpret_cast<float *>(wf.sum + slot);
+                float *dst = reinterpret_cast<float *>(wf.acc + 2 * slot + 1);
                 atomicAdd(dst + 0, c.x / inv_L_div);
                 atomicAdd(dst + 1, c.y / inv_L_div);
                 atomicAdd(dst + 2, c.z / inv_L_div);
             }
         } else if (slot >= 0) {
-            float *dst = reinterpret_cast<float *>(wf.sum + slot);
+            float *dst = reinterpret_cast<float *>(wf.acc + 2 * slot + 1);
             if (c.x != 0.f)
                 atomicAdd(dst + 0, c.x / inv_L_div);
             if (c.y != 0.f)
@@ -446,6 +508,118 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
     }
     if (COUNT)
         flush_counts(tc, nrays, wf.trace_counts + 3, ntraced, wf.trace_counts + 6);
+}
+
+// ---- counting sort of a queue by key (PT_SORT_BUCKETS buckets) ------------------------------------------------------
+// Three launches: histogram (one atomic per distinct key of a warp), exclusive scan of the counters in chunks of
+// PT_SORT_CHUNK (chunk totals aside), scatter (the chunk totals are scanned again by every block: <= 1024 values).
+// Entries of one bucket keep no particular order; the film does not depend on queue order (per-slot sums, Philox
+// keyed by pixel and sample).
+__global__ void __launch_bounds__(kThreads) k_sort_hist(const uint32_t *__restrict__ keys, const int32_t *__restrict__ count,
+                                                        uint32_t *__restrict__ hist)
+{
+    const int n = *count;
+    const int lane = threadIdx.x & 31;
+    for (int base = blockIdx.x * kThreads; base < n; base += gridDim.x * kThreads) {
+        const int i = base + threadIdx.x;
+        const bool live = i < n;
+        const uint32_t key = live ? keys[i] : 0xffffffffu;
+        const unsigned peers = __match_any_sync(0xffffffffu, key);
+        if (live && lane == __ffs(peers) - 1)
+            atomicAdd(hist + key, (uint32_t)__popc(peers));
+    }
+}
+
+__global__ void __launch_bounds__(1024) k_sort_scan(uint32_t *__restrict__ hist)
+{
+    // one block per chunk of PT_SORT_CHUNK counters, two per thread
+    __shared__ uint32_t s_warp[32];
+    uint32_t *h = hist + (size_t)blockIdx.x * PT_SORT_CHUNK;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint32_t a = h[2 * t], b = h[2 * t + 1];
+    uint32_t v = a + b, incl = v;
+    for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t u = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off)
+            incl += u;
+    }
+    if (lane == 31)
+        s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = s_warp[lane], wi = w;
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t u = __shfl_up_sync(0xffffffffu, wi, off);
+            if (lane >= off)
+                wi += u;
+        }
+        s_warp[lane] = wi - w; // exclusive
+        if (lane == 31)
+            hist[PT_SORT_BUCKETS + blockIdx.x] = wi; // chunk total
+    }
+    __syncthreads();
+    const uint32_t excl = s_warp[warp] + incl - v;
+    h[2 * t] = excl;
+    h[2 * t + 1] = excl + a;
+}
+
+__global__ void __launch_bounds__(kThreads) k_sort_scatter(const uint32_t *__restrict__ keys, const int32_t *__restrict__ raw,
+                                                           const int32_t *__restrict__ count, uint32_t *__restrict__ hist,
+                                                           int32_t *__restrict__ dst)
+{
+    constexpr int kChunks = PT_SORT_BUCKETS / PT_SORT_CHUNK;
+    static_assert(kChunks <= 4096, "chunk totals are scanned by one block");
+    __shared__ uint32_t s_chunk[kChunks];
+    __shared__ uint32_t s_part[kThreads / 32];
+    const int n = *count;
+    if ((int)(blockIdx.x * kThreads) >= n)
+        return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    {
+        // exclusive scan of the chunk totals: kChunks / kThreads consecutive values per thread
+        constexpr int per = (kChunks + kThreads - 1) / kThreads;
+        uint32_t v[per], sum = 0;
+#pragma unroll
+        for (int k = 0; k < per; k++) {
+            const int c = threadIdx.x * per + k;
+            v[k] = c < kChunks ? hist[PT_SORT_BUCKETS + c] : 0u;
+            sum += v[k];
+        }
+        uint32_t incl = sum;
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t u = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off)
+                incl += u;
+        }
+        if (lane == 31)
+            s_part[warp] = incl;
+        __syncthreads();
+        uint32_t before = 0;
+        for (int w2 = 0; w2 < warp; w2++)
+            before += s_part[w2];
+        uint32_t run = before + incl - sum;
+#pragma unroll
+        for (int k = 0; k < per; k++) {
+            const int c = threadIdx.x * per + k;
+            if (c < kChunks)
+                s_chunk[c] = run;
+            run += v[k];
+        }
+        __syncthreads();
+    }
+    for (int base = blockIdx.x * kThreads; base < n; base += gridDim.x * kThreads) {
+        const int i = base + threadIdx.x;
+        const bool live = i < n;
+        const uint32_t key = live ? keys[i] : 0xffffffffu;
+        const unsigned peers = __match_any_sync(0xffffffffu, key);
+        const int leader = __ffs(peers) - 1;
+        uint32_t first = 0;
+        if (live && lane == leader)
+            first = atomicAdd(hist + key, (uint32_t)__popc(peers)) + s_chunk[key / PT_SORT_CHUNK];
+        first = __shfl_sync(0xffffffffu, first, leader);
+        if (live)
+            dst[first + __popc(peers & ((1u << lane) - 1u))] = raw[i];
+    }
 }
 
 // framebuffer[j][i] += de_nan(col): one thread per pixel walks the samples of the batch in order, so the film is
@@ -463,7 +637,7 @@ __global__ void __launch_bounds__(kThreads) k_accumulate(RenderParams rp, Wavefr
             cq = film.csq[pix];
         }
         for (int k = 0; k < nsamp; k++) {
-            float4 v = wf.sum[(size_t)k * wf.npix + pix];
+            float4 v = wf.acc[2 * ((size_t)k * wf.npix + pix) + 1];
             float x = is_nan(v.x) ? 0.f : v.x, y = is_nan(v.y) ? 0.f : v.y, z = is_nan(v.z) ? 0.f : v.z; // de_nan
             acc.x += x;
             acc.y += y;
@@ -767,6 +941,16 @@ void launch_nee(const PtSceneView &s, const RenderParams &rp, const Wavefront &w
     else
         PT_LAUNCH_NEE(false, false, false);
 #undef PT_LAUNCH_NEE
+}
+
+void launch_sort_queue(const Wavefront &wf, const uint32_t *keys, const int32_t *raw, int32_t *dst, int count_index,
+                       const LaunchCfg &lc, cudaStream_t st)
+{
+    const int32_t *count = wf.counters + count_index;
+    cudaMemsetAsync(wf.sort_hist, 0, sizeof(uint32_t) * PT_SORT_BUCKETS, st);
+    k_sort_hist<<<lc.blocks, kThreads, 0, st>>>(keys, count, wf.sort_hist);
+    k_sort_scan<<<PT_SORT_BUCKETS / PT_SORT_CHUNK, PT_SORT_CHUNK / 2, 0, st>>>(wf.sort_hist);
+    k_sort_scatter<<<lc.blocks, kThreads, 0, st>>>(keys, raw, count, wf.sort_hist, dst);
 }
 
 void launch_accumulate(const RenderParams &rp, const Wavefront &wf, const Film &film, int n_rows, cudaStream_t st)

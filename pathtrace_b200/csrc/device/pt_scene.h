@@ -82,6 +82,10 @@ struct alignas(16) PtTexel {
     float r, g, b, a;
 };
 
+#ifndef PT_SORT_CELL_BITS
+#define PT_SORT_CELL_BITS 6 /* Morton bits per axis of the coherence-sort key (kernels.cu) */
+#endif
+
 struct PtCamera {
     V3 origin, lower_left, horizontal, vertical, u, v;
     float lens_radius;
@@ -106,6 +110,9 @@ struct PtSceneView {
     int32_t emit_needs_p; // some emitter has a non-constant texture: shadow hits must report p (else only the normal)
     int32_t n_media; // instances wrapped in a constant_medium; 0 selects the kernels compiled without that branch
     int32_t n_light_boxes; // n_lights when every light is a rect or a sphere (and there are <= 8), else 0
+    // coherence sort keys (kernels.cu sort_key_*): cell = (p - sort_lo) * sort_scale * 2^bits, clamped; the bounds are those of
+    // the instances that are not media (a scene-wide mist would make every cell cover the whole scene)
+    float sort_lo[3], sort_scale[3];
     PtCamera cam;
 };
 

@@ -1,7 +1,7 @@
 // wavefront.cuh -- device-side layout of one wavefront batch and the launch interface of the kernels.
 //
 // A batch renders `nsamp` samples of every pixel: slot = s_local * npix + pixel.  All per-path state lives in
-// float4 SoA arrays indexed by slot (one 128-bit access per field); the kernels of one bounce are connected by
+// float4 pairs indexed by slot (one 32-byte sector per record); the kernels of one bounce are connected by
 // queues of slot indices, compacted with warp ballots and a block prefix sum in shared memory:
 //
 //   raygen -> [ extend -> shade{miss,diffuse,dielectric,light,isotropic} -> nee ] x bounces -> accumulate
@@ -30,17 +30,23 @@ struct BatchCtl {           // device-resident, advanced by the tally kernel at 
 };
 
 struct Wavefront {
-    float4 *ray_o; // o.xyz, last_bsdf_pdf
-    float4 *ray_d; // d.xyz, -
-    float4 *beta;  // beta.xyz, -
-    float4 *att;   // attenuation.xyz of the previous vertex, -
-    float4 *hit_p; // p.xyz, instance (int bits; -1 = miss)
-    float4 *hit_n; // n.xyz, t
-    float4 *nee_w; // W.xyz = attenuation*beta, material kind (int bits)
-    float4 *sum;   // radiance of the sample so far
+    // Per-slot state in PAIRS of float4 = one 32-byte DRAM sector per record: once the queues are sorted for ray
+    // coherence a kernel visits slots in no particular order, and a 16-byte field on its own would cost a whole sector.
+    float4 *ray; // [2 slot] = o.xyz, last_bsdf_pdf      [2 slot + 1] = d.xyz, -
+    float4 *thr; // [2 slot] = beta.xyz, -               [2 slot + 1] = attenuation.xyz of the previous vertex, -
+    float4 *hit; // [2 slot] = p.xyz, instance | face    [2 slot + 1] = n.xyz, t
+    float4 *acc; // [2 slot] = W.xyz = attenuation*beta, material kind    [2 slot + 1] = radiance of the sample so far
     int32_t *q_ext[2];
     int32_t *q_kind[SK_COUNT];
     int32_t *q_nee;
+    // Coherence sort between bounces (sort_cells > 0; scenes walked through the BVH): k_shade appends to the RAW queues
+    // together with a key per entry -- direction octant | Morton code of the ray origin for the next extension
+    // rays, Morton code of the vertex for the light samples -- and a counting sort (k_sort_*) writes q_ext / q_nee in
+    // key order, so that the 32 rays of a warp start close together and head the same way.
+    int32_t *q_raw_ext, *q_raw_nee;
+    uint32_t *key_ext, *key_nee;
+    uint32_t *sort_hist;   // PT_SORT_BUCKETS counters + PT_SORT_BUCKETS / PT_SORT_CHUNK chunk totals
+    int32_t sort_on;
     int32_t *counters; // (max_bounces + 2) rows of CNT_ROW
     BatchCtl *ctl;
     // traced paths (config.trace_probability > 0, else null): slot -> path id, per path {pixel, sample lo, sample hi,
@@ -56,6 +62,13 @@ struct Wavefront {
     int32_t capacity; // slots
     uint32_t npix_mul, npix_shr; // slot / npix == umulhi(slot, npix_mul) >> npix_shr (npix_mul == 0: npix == 1)
 };
+
+#ifndef PT_SORT_DIR_BITS
+#define PT_SORT_DIR_BITS 3                                     /* direction bin: 3 = octant, 2n = n x n-bit octahedral grid */
+#endif
+#define PT_SORT_BITS (3 * PT_SORT_CELL_BITS + PT_SORT_DIR_BITS)
+#define PT_SORT_BUCKETS (1 << PT_SORT_BITS)
+#define PT_SORT_CHUNK 2048                                    /* counters scanned by one block */
 
 struct Film {
     float4 *accum; // per pixel radiance sums (row 0 = image bottom), .w unused
@@ -77,6 +90,9 @@ void launch_shade(const PtSceneView &s, const RenderParams &rp, const Wavefront 
                   const LaunchCfg &lc, cudaStream_t st);
 void launch_nee(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, const LaunchCfg &lc,
                 cudaStream_t st);
+// counting sort of a raw queue by key into `dst`; the entry count is read from counters[count_index] on the device
+void launch_sort_queue(const Wavefront &wf, const uint32_t *keys, const int32_t *raw, int32_t *dst, int count_index,
+                       const LaunchCfg &lc, cudaStream_t st);
 void launch_accumulate(const RenderParams &rp, const Wavefront &wf, const Film &film, int n_rows, cudaStream_t st);
 
 // closest-hit batch (b200pt_trace_batch): rays n x 8 floats, hits n x b200pt_hit

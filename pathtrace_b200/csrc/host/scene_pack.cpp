@@ -57,6 +57,25 @@ PackedScene pack_scene(const FlatScene &f)
         boxes[i] = instance_bounds(src);
     }
     out.n_media = media;
+    {
+        // cells of the coherence sort: the bounds of everything that is not a medium (all instances if nothing else)
+        float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
+        for (int pass = 0; pass < 2 && !(lo[0] <= hi[0]); pass++)
+            for (int i = 0; i < n; i++) {
+                if (pass == 0 && (f.instances[i].flags & B200PT_INST_MEDIUM))
+                    continue;
+                for (int k = 0; k < 3; k++) {
+                    if (boxes[i].lo[k] > -1e30f && boxes[i].lo[k] < lo[k])
+                        lo[k] = boxes[i].lo[k];
+                    if (boxes[i].hi[k] < 1e30f && boxes[i].hi[k] > hi[k])
+                        hi[k] = boxes[i].hi[k];
+                }
+            }
+        for (int k = 0; k < 3; k++) {
+            out.sort_bounds[k] = lo[k] <= hi[k] ? lo[k] : 0.f;
+            out.sort_bounds[3 + k] = lo[k] <= hi[k] ? hi[k] : 1.f;
+        }
+    }
     // World bounds of the lights, for the horizon test of pt_shade.h lights_below_horizon: only lights whose samples
     // point AT them (rect::random, sphere::random); a box or medium in the light list samples the fixed direction
     // (1, 0, 0) (hittable.h:28) and switches the test off.
@@ -152,6 +171,11 @@ pt::PtSceneView PackedScene::host_view(const FlatScene &f) const
         if (m.kind == B200PT_MAT_DIFFUSE_LIGHT &&
             !(m.texture >= 0 && m.texture < (int)f.textures.size() && f.textures[m.texture].kind == B200PT_TEX_CONSTANT))
             v.emit_needs_p = 1;
+    for (int k = 0; k < 3; k++) {
+        const float ext = sort_bounds[3 + k] - sort_bounds[k];
+        v.sort_lo[k] = sort_bounds[k];
+        v.sort_scale[k] = ext > 0.f ? 1.0f / ext : 0.f; // position -> [0, 1) of the sort bounds
+    }
     v.cam.origin = to_v3(f.camera.origin);
     v.cam.lower_left = to_v3(f.camera.lower_left);
     v.cam.horizontal = to_v3(f.camera.horizontal);

@@ -20,6 +20,7 @@ struct PackedScene {
     std::vector<int32_t> emitters;     // instances whose hit material is a diffuse_light, ascending
     std::vector<pt::PtBox> light_boxes; // world bounds per light (flat.lights order); empty: the horizon test is off
     int n_media = 0;
+    float sort_bounds[6] = {0, 0, 0, 1, 1, 1}; // bounds of the non-medium instances (coherence sort cells)
     // a view whose pointers refer to THIS object's host vectors and to `flat`'s material/texture/light arrays
     pt::PtSceneView host_view(const FlatScene &flat) const;
 };

@@ -280,7 +280,7 @@ class Wavefront:
         p = _capi.Profile()
         check(lib().b200pt_render_profile(self._h, C.byref(p)))
         out = {"ms": dict(zip(_capi.KERNEL_NAMES, p.ms[:])), "launches": dict(zip(_capi.KERNEL_NAMES, p.launches[:]))}
-        for k in ("ext_rays", "ext_boxes", "ext_prims", "nee_rays", "nee_boxes", "nee_prims", "nee_traced"):
+        for k in ("ext_rays", "ext_boxes", "ext_prims", "nee_rays", "nee_boxes", "nee_prims", "nee_traced", "nee_queued"):
             out[k] = getattr(p, k)
         return out
 
