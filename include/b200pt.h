@@ -159,6 +159,20 @@ typedef struct b200pt_config {
                                standard path tracer over the same scene (device/pt_corrected.h): specular metal with
                                fuzz, refracting glass, emission counted once, outgoing-cosine throughput, 1/n light
                                pick.  metal.fuzz travels in b200pt_material.power. */
+    /* Multi-GPU inside the library (config.json "devices": N or "device_ids": [...]); the reference's own analogue is
+     * the spp split of its worker threads (renderer.h:352-360: config.samples / N_THREADS each).  device_count <= 1:
+     * one GPU, `device`.  Otherwise the scene is replicated on device_ids[0 .. device_count), `samples` are split over
+     * them by global sample index (same film for any device count), one host thread and stream per device drive the
+     * wavefront batches, and the per-device films are summed on device_ids[0] over NVLink peer loads (falling back to
+     * peer copies) in the kernel that also reduces the luminance for the tonemap. */
+    int32_t device_count;
+    int32_t device_ids[8];
+    /* 0: b200pt_render_poll advances the render itself, `max_batches` at a time, and returns when they are done (the
+     * caller paces the work; what tests and bench.py use).  1: b200pt_render_start behaves like Renderer::start_render
+     * (renderer.h:553-603): worker threads start rendering at once and the call returns; b200pt_render_poll then only
+     * REPORTS progress (it never blocks on the GPU beyond a batch boundary), read / tonemap / write_ppm return a
+     * consistent snapshot of the film while the render goes on, b200pt_render_wait blocks until it is done. */
+    int32_t async_render;
 } b200pt_config;
 
 typedef struct b200pt_scene b200pt_scene;
@@ -238,6 +252,9 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
 /* sync_progress/is_done (renderer.h:605-625): advances the render by at most `max_batches` wavefront batches
  * (0 = run to completion) and reports progress. */
 int b200pt_render_poll(b200pt_render *render, int32_t max_batches, b200pt_progress *progress);
+/* Blocks until every batch has been rendered (the join the reference's finalize() implies, renderer.h:693-699) and
+ * reports the final progress.  Works in both modes (async_render = 0: renders whatever is left). */
+int b200pt_render_wait(b200pt_render *render, b200pt_progress *progress);
 /* Renderer::framebuffer (renderer.h:141): per-pixel radiance SUMS, H x W x 3 float32, row 0 = image bottom.
  * spp_done receives the number of samples per pixel the sums hold. */
 int b200pt_render_read(b200pt_render *render, float *rgb_sums, int64_t *spp_done);

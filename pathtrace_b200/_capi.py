@@ -64,7 +64,8 @@ class Config(C.Structure):
                 ("seed", C.c_uint64), ("sample_offset", C.c_int64), ("device", C.c_int32),
                 ("batch_samples", C.c_int32), ("stats_clamp", C.c_float), ("profile", C.c_int32),
                 ("trace_probability", C.c_float), ("trace_max_paths", C.c_int32),
-                ("physically_corrected", C.c_int32)]
+                ("physically_corrected", C.c_int32), ("device_count", C.c_int32), ("device_ids", C.c_int32 * 8),
+                ("async_render", C.c_int32)]
 
 
 class Progress(C.Structure):
@@ -103,6 +104,7 @@ SIGNATURES = {
     "b200pt_philox4x32_10": (C.c_int, [C.c_int32, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200pt_render_start": (C.c_int, [C.c_void_p, C.POINTER(Config), C.POINTER(C.c_void_p)]),
     "b200pt_render_poll": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(Progress)]),
+    "b200pt_render_wait": (C.c_int, [C.c_void_p, C.POINTER(Progress)]),
     "b200pt_render_read": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]),
     "b200pt_render_read_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200pt_render_device_buffer": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),

@@ -11,6 +11,8 @@
 #include <iostream>
 #include <sstream>
 #include <string>
+#include <algorithm>
+#include <thread>
 
 static std::string slurp(const std::string &path)
 {
@@ -46,7 +48,8 @@ int main(int argc, char *argv[])
               << "px^2" << std::endl;
     std::cout << "with " << config.samples << " samples per pixel, that sets a minimum number of camera rays at "
               << min_camera_rays << "\n\n";
-    std::cout << "using " << config.threads << " threads (ignored: " << b200pt_version() << ")\n";
+    std::cout << "using " << config.threads << " threads (ignored: " << b200pt_version() << ", "
+              << (config.device_count > 1 ? config.device_count : 1) << " GPU(s))\n";
     std::cout << "reading scene data" << std::endl;
     std::string scene_text = slurp(scene_path);
 
@@ -57,28 +60,46 @@ int main(int argc, char *argv[])
     auto t2 = std::chrono::high_resolution_clock::now();
     std::cout << "time taken to build bvh " << std::chrono::duration<double>(t2 - t1).count() << std::endl;
 
+    // start_render (renderer.h:553-603) returns at once: one worker thread per GPU renders in the background
+    // ("devices": N in config.json puts N GPUs on the frame); this thread is main()'s polling loop (main.cpp:158-163)
+    config.async_render = 1;
     b200pt_render *render = nullptr;
     if (b200pt_render_start(scene, &config, &render))
         die("render_start");
     auto start = std::chrono::high_resolution_clock::now();
     b200pt_progress pr{};
-    auto last_write = start;
-    while (!pr.done) {
-        // sync_progress (renderer.h:605-620): progress line + tonemapped PPM rewrite, at most every 0.5 s
-        if (b200pt_render_poll(render, 1, &pr))
+    // tests shorten the 0.5 s of main.cpp:162 and keep every preview: B200PT_CLI_POLL_MS, B200PT_CLI_KEEP_PREVIEWS=<prefix>
+    const char *poll_env = std::getenv("B200PT_CLI_POLL_MS");
+    const int poll_ms = poll_env ? std::max(1, atoi(poll_env)) : 500;
+    const char *keep = std::getenv("B200PT_CLI_KEEP_PREVIEWS");
+    int previews = 0;
+    while (true) {
+        // sync_progress (renderer.h:605-620): progress line, then the film so far tonemapped with 1 + done / pixels
+        // samples and written over the PPM
+        if (b200pt_render_poll(render, 0, &pr))
             die("render_poll");
+        if (pr.done)
+            break;
         auto now = std::chrono::high_resolution_clock::now();
         double elapsed = std::chrono::duration<double>(now - start).count();
         float rate = (float)(pr.samples_done / (elapsed > 0 ? elapsed : 1e-9));
         std::cout << "samples left" << std::setw(20) << (pr.samples_total - pr.samples_done) << " rate " << std::setw(10)
                   << rate << " time left " << std::setw(5) << (pr.samples_total - pr.samples_done) / rate
                   << "                                           " << '\r' << std::flush;
-        if (!pr.done && std::chrono::duration<double>(now - last_write).count() >= 0.5) {
-            if (b200pt_render_write_ppm(render, 1 + pr.samples_done / total_pixels, ppm_path))
+        const long n_preview = 1 + pr.samples_done / total_pixels;
+        if (b200pt_render_write_ppm(render, n_preview, ppm_path))
+            die("write_ppm");
+        if (keep) {
+            const std::string copy = std::string(keep) + std::to_string(previews) + ".ppm";
+            if (b200pt_render_write_ppm(render, n_preview, copy.c_str()))
                 die("write_ppm");
-            last_write = now;
+            std::cout << "\npreview " << previews << " samples " << n_preview << std::endl;
         }
+        previews++;
+        std::this_thread::sleep_for(std::chrono::milliseconds(poll_ms));
     }
+    if (b200pt_render_wait(render, &pr))
+        die("render_wait");
     std::cout << " done\n";
 
     // finalize (renderer.h:693-727)

@@ -812,6 +812,50 @@ __global__ void __launch_bounds__(kThreads) k_luminance(const float4 *__restrict
     }
 }
 
+// Multi-GPU: the films of all devices summed into `dst` on this device, in device order (a fixed order: the total is
+// bit-reproducible), reading the other devices' buffers in place over NVLink peer loads (or their staged copies).  With
+// max_total != null the same pass reduces calculate_luminance's max / total (helpers.h:146-168) of the summed film, so the
+// tonemap that follows needs no second pass over it.
+__global__ void __launch_bounds__(kThreads) k_combine(FilmSources fs, int npix, float4 *__restrict__ dst, float inv_n,
+                                                      float *max_total)
+{
+    float mx = 0.f, tot = 0.f;
+    for (int i = blockIdx.x * kThreads + threadIdx.x; i < npix; i += gridDim.x * kThreads) {
+        float4 a = fs.src[0][i];
+        for (int d = 1; d < fs.n; d++) {
+            const float4 b = fs.src[d][i];
+            a.x += b.x, a.y += b.y, a.z += b.z, a.w += b.w;
+        }
+        dst[i] = a;
+        if (max_total) {
+            V3 c = v3(is_nan(a.x) ? 0.f : a.x, is_nan(a.y) ? 0.f : a.y, is_nan(a.z) ? 0.f : a.z) * inv_n;
+            const float f = length(c);
+            tot += f;
+            mx = fmaxf(mx, f);
+        }
+    }
+    if (!max_total)
+        return;
+    for (int off = 16; off > 0; off >>= 1) {
+        mx = fmaxf(mx, __shfl_down_sync(0xffffffffu, mx, off));
+        tot += __shfl_down_sync(0xffffffffu, tot, off);
+    }
+    __shared__ float s_mx[kWarps], s_tot[kWarps];
+    if ((threadIdx.x & 31) == 0) {
+        s_mx[threadIdx.x >> 5] = mx;
+        s_tot[threadIdx.x >> 5] = tot;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < kWarps; w++) {
+            mx = fmaxf(mx, s_mx[w]);
+            tot += s_tot[w];
+        }
+        atomicMax(reinterpret_cast<int *>(max_total), __float_as_int(mx));
+        atomicAdd(max_total + 1, tot);
+    }
+}
+
 // film sums float4 -> packed rgb floats (what b200pt_render_read hands to the caller)
 __global__ void __launch_bounds__(kThreads) k_pack_rgb(const float4 *__restrict__ accum, int npix, float *__restrict__ rgb)
 {
@@ -997,6 +1041,16 @@ void launch_luminance(const float4 *accum, int npix, float inv_n, float *max_tot
     if (blocks > 148 * 8)
         blocks = 148 * 8;
     k_luminance<<<blocks, kThreads, 0, st>>>(accum, npix, inv_n, max_total);
+}
+
+void launch_combine(const FilmSources &fs, int npix, float4 *dst, float inv_n, float *max_total, cudaStream_t st)
+{
+    if (max_total)
+        cudaMemsetAsync(max_total, 0, 2 * sizeof(float), st);
+    int blocks = (npix + kThreads - 1) / kThreads;
+    if (blocks > 148 * 8)
+        blocks = 148 * 8;
+    k_combine<<<blocks, kThreads, 0, st>>>(fs, npix, dst, inv_n, max_total);
 }
 
 void launch_pack_rgb(const float4 *accum, int npix, float *rgb, cudaStream_t st)

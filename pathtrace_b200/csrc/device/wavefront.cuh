@@ -104,6 +104,13 @@ void launch_philox(const uint32_t *in, size_t n, uint32_t *out, cudaStream_t st)
 
 // film: luminance reduce (max, total of |sum/n|) and tonemap to bytes (top row first)
 void launch_luminance(const float4 *accum, int npix, float inv_n, float *max_total /* [2] */, cudaStream_t st);
+// multi-GPU: dst = sum of up to 8 films (device order), optionally with the luminance reduce of the sum fused in
+struct FilmSources {
+    const float4 *src[8];
+    int n;
+};
+void launch_combine(const FilmSources &fs, int npix, float4 *dst, float inv_n, float *max_total /* [2] or null */,
+                    cudaStream_t st);
 void launch_pack_rgb(const float4 *accum, int npix, float *rgb, cudaStream_t st);
 void launch_tonemap(const float4 *accum, int width, int height, float inv_n, float exposure_mul, float max_lum,
                     uint8_t *rgb, cudaStream_t st);

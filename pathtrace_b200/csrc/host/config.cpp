@@ -58,7 +58,26 @@ ParsedConfig parse_config(const Json &j)
     c.seed = (uint64_t)j.value("seed", 0L);
     c.device = (int32_t)j.value("device", 0);
     c.batch_samples = (int32_t)j.value("batch_samples", 0);
-    out.device_count = (int32_t)j.value("device_count", 1);
+    // "devices": N renders on GPUs 0 .. N-1, "device_ids": [a, b, ...] on the listed ones (the film is combined on the
+    // first); like the reference's "threads", a scheduling key that does not change the image
+    out.device_count = (int32_t)j.value("devices", (long)j.value("device_count", 1));
+    if (j.contains("device_ids") && j["device_ids"].is_array()) {
+        const Json &ids = j["device_ids"];
+        if (ids.size() < 1 || ids.size() > 8)
+            throw std::runtime_error("config: \"device_ids\" must list 1 to 8 devices");
+        c.device_count = (int32_t)ids.size();
+        for (size_t k = 0; k < ids.size(); k++)
+            c.device_ids[k] = (int32_t)ids.at(k).as_double();
+        c.device = c.device_ids[0];
+    } else if (out.device_count > 1) {
+        if (out.device_count > 8)
+            throw std::runtime_error("config: \"devices\" must be at most 8");
+        c.device_count = out.device_count;
+        for (int k = 0; k < out.device_count; k++)
+            c.device_ids[k] = c.device + k;
+    }
+    out.device_count = c.device_count > 1 ? c.device_count : 1;
+    c.async_render = j.value("async_render", false) ? 1 : 0;
     // config.h:122-131: `long min_camera_rays = samples * film.total_pixels`
     c.trace_probability = 0.f;
     if (out.should_trace_paths)

@@ -60,8 +60,18 @@ class Config:
         return getattr(self.c, name)
 
     def replace(self, **kw):
+        """A copy with fields of b200pt_config replaced; `devices=[0, 1, ...]` sets device_count / device_ids / device."""
         c = _CConfig()
         C.memmove(C.byref(c), C.byref(self.c), C.sizeof(c))
+        devices = kw.pop("devices", None)
+        if devices is not None:
+            devices = list(devices)
+            if not 1 <= len(devices) <= 8:
+                raise ValueError("1 to 8 devices")
+            c.device = devices[0]
+            c.device_count = len(devices) if len(devices) > 1 else 0
+            for k, d in enumerate(devices):
+                c.device_ids[k] = d
         for k, v in kw.items():
             setattr(c, k, v)
         return Config(c, self.scene_path, self.ppm_output_path, self.traced_paths_output_path,
@@ -231,10 +241,14 @@ class Wavefront:
     def is_done(self):
         return bool(self.progress.done)
 
+    def wait(self):
+        """Block until every batch is rendered (both modes) and refresh `progress`."""
+        check(lib().b200pt_render_wait(self._h, C.byref(self.progress)))
+        return self.progress
+
     def finalize(self, ppm_path=None):
         """Run to completion; optionally write the PPM (renderer.h:693-727).  Returns the rate report."""
-        while not self.is_done():
-            self.sync_progress(0)
+        self.wait()
         p = self.progress
         secs = p.seconds if p.seconds > 0 else float("nan")
         report = {

@@ -116,7 +116,8 @@ class _CConfig(C.Structure):  # mirrors b200pt_config (include/b200pt.h)
                 ("seed", C.c_uint64), ("sample_offset", C.c_int64), ("device", C.c_int32),
                 ("batch_samples", C.c_int32), ("stats_clamp", C.c_float), ("profile", C.c_int32),
                 ("trace_probability", C.c_float), ("trace_max_paths", C.c_int32),
-                ("physically_corrected", C.c_int32)]
+                ("physically_corrected", C.c_int32), ("device_count", C.c_int32), ("device_ids", C.c_int32 * 8),
+                ("async_render", C.c_int32)]
 
 
 INTEGRATORS = {"iterative nee path tracing": 4, "recursive path tracing": 0}
