@@ -270,6 +270,23 @@ int b200pt_render_write(b200pt_render *render, const float *rgba_sums, int64_t s
  * config.samples; sync_progress 1 + done/pixels). */
 int b200pt_render_tonemap(b200pt_render *render, int64_t n_samples, uint8_t *rgb, float *max_luminance,
                           float *avg_luminance);
+/* Allocation-free tonemap.  NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same result
+ * as b200pt_render_tonemap -- calculate_luminance + output_to_file on a film of sums -- on buffers the caller owns:
+ *   d_rgba_sums  DEVICE, H x W float4 radiance sums, row 0 = image bottom (the layout of b200pt_render_device_buffer)
+ *   d_rgb        DEVICE, H x W x 3 bytes out, TOP row first
+ *   stream       a cudaStream_t on `device` (NULL = the default stream); the three kernels are enqueued on it
+ *   max_luminance / avg_luminance  HOST, optional.  Both NULL: nothing is copied back and the call returns without
+ *                synchronising (the white point stays on the device); otherwise the call waits for the stream.
+ * It calls no cudaMalloc, cudaFree or allocating library routine: the scratch of the luminance reduce is a file-scope
+ * `static __device__` array in the library (128.25 KiB, held by every GPU that loads the library until the process exits),
+ * one partial per 1024 pixels.  LIMIT: width x height <= 16 777 216 pixels (16384 partials; twice a 3840 x 2160 film);
+ * a larger film is refused with B200PT_ERR_INVALID and a message naming the limit.  Every call on a GPU shares that one
+ * array: calls whose kernels overlap on the same GPU (two streams, two threads) race -- serialise them.  The array keeps
+ * the previous call's contents; no cell needs clearing, every cell a call reads it has written first.  The luminance
+ * total is summed in a fixed order (bit-reproducible; b200pt_render_tonemap's uses float atomics). */
+int b200pt_tonemap_static(int32_t device, const void *d_rgba_sums, int32_t width, int32_t height, int64_t n_samples,
+                          float exposure, void *d_rgb, void *stream, float *max_luminance, float *avg_luminance);
 /* Writes "P6\nW H\n255\n" + payload (renderer.h:26-53). */
 int b200pt_render_write_ppm(b200pt_render *render, int64_t n_samples, const char *path);
 

@@ -110,6 +110,8 @@ SIGNATURES = {
     "b200pt_render_device_buffer": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "b200pt_render_write": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
     "b200pt_render_tonemap": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "b200pt_tonemap_static": (C.c_int, [C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_int64, C.c_float, C.c_void_p,
+                                        C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "b200pt_render_write_ppm": (C.c_int, [C.c_void_p, C.c_int64, C.c_char_p]),
     "b200pt_render_paths": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -1446,6 +1446,34 @@ int b200pt_render_tonemap(b200pt_render *r, int64_t n_samples, uint8_t *rgb, flo
     });
 }
 
+int b200pt_tonemap_static(int32_t device, const void *d_rgba_sums, int32_t width, int32_t height, int64_t n_samples,
+                          float exposure, void *d_rgb, void *stream, float *max_luminance, float *avg_luminance)
+{
+    // no cudaMalloc / cudaFree / allocating routine anywhere on this path: the scratch is kernels.cu's static array
+    if (!d_rgba_sums || !d_rgb || width <= 0 || height <= 0 || n_samples <= 0)
+        return fail(B200PT_ERR_INVALID, "b200pt_tonemap_static: bad argument");
+    const long long npix = (long long)width * (long long)height;
+    if (npix > (long long)PT_STATIC_MAX_PIXELS)
+        return fail(B200PT_ERR_INVALID, "b200pt_tonemap_static: film of " + std::to_string(width) + " x " +
+                                            std::to_string(height) + " = " + std::to_string(npix) +
+                                            " pixels exceeds the static scratch of " +
+                                            std::to_string((long long)PT_STATIC_MAX_PIXELS) +
+                                            " pixels (use b200pt_render_tonemap, which allocates)");
+    return guarded([&] {
+        select_device(device);
+        // col /= float(samples) is a multiplication by float(1.0 / t) (vec3.h:181-189); col *= 16 + exposure (renderer.h:37)
+        const float inv_n = (float)(1.0 / (float)n_samples);
+        float lum[2] = {0.f, 0.f};
+        const bool want = max_luminance || avg_luminance;
+        CK(pt::launch_tonemap_static(device, (const float4 *)d_rgba_sums, width, height, inv_n, 16 + exposure,
+                                     (uint8_t *)d_rgb, want ? lum : nullptr, (cudaStream_t)stream));
+        if (max_luminance)
+            *max_luminance = lum[0];
+        if (avg_luminance) // helpers.h:167: total / (total_pixels * n_samples) (sic: divided by n twice)
+            *avg_luminance = lum[1] / ((float)npix * (float)n_samples);
+    });
+}
+
 int b200pt_render_write_ppm(b200pt_render *r, int64_t n_samples, const char *path)
 {
     if (!r || !path)

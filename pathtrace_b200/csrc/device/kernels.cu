@@ -13,6 +13,7 @@
 #include "wavefront.cuh"
 
 #include <algorithm>
+#include <mutex>
 
 namespace pt {
 
@@ -907,6 +908,105 @@ __global__ void __launch_bounds__(kThreads) k_tonemap(const float4 *__restrict__
     }
 }
 
+// ---- allocation-free tonemap (b200pt_tonemap_static) -----------------------------------------------------------------
+// calculate_luminance + output_to_file for callers that may not allocate (CUDA graph capture, serving loops): the scratch
+// of the luminance reduce lives in a file-scope __device__ array instead of a cudaMalloc'ed block.  Layout:
+//   [2 b], [2 b + 1]              max / total of |sum / n| over the pixels of tile b (PT_STATIC_TILE pixels each)
+//   [2 PT_STATIC_MAX_TILES + 0/1] max / total over the film (written by k_static_lum_final, read by k_static_tonemap)
+// Every cell a call reads was written earlier in the same call, so nothing has to start at zero and the contents the
+// previous call left behind are never seen; the totals are summed in a fixed order (bit-reproducible, unlike the atomics
+// of k_luminance).  Every GPU that loads the library holds the array (PT_STATIC_SCRATCH_FLOATS * 4 bytes = 128.25 KiB)
+// until the process exits.  All calls share it: two calls that overlap on one GPU race.
+constexpr int kStaticTile = PT_STATIC_TILE;
+static __device__ __align__(256) float g_static_scratch[PT_STATIC_SCRATCH_FLOATS];
+
+__global__ void __launch_bounds__(kThreads) k_static_lum_partials(const float4 *__restrict__ accum, int npix, float inv_n,
+                                                                  float *__restrict__ scratch)
+{
+    float mx = 0.f, tot = 0.f;
+    const int base = blockIdx.x * kStaticTile;
+#pragma unroll
+    for (int k = 0; k < kStaticTile / kThreads; k++) { // fixed order within a thread
+        const int i = base + k * kThreads + threadIdx.x;
+        if (i < npix) {
+            const float4 v = accum[i];
+            V3 c = v3(is_nan(v.x) ? 0.f : v.x, is_nan(v.y) ? 0.f : v.y, is_nan(v.z) ? 0.f : v.z) * inv_n;
+            const float f = length(c);
+            tot += f;
+            mx = fmaxf(mx, f);
+        }
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        mx = fmaxf(mx, __shfl_down_sync(0xffffffffu, mx, off));
+        tot += __shfl_down_sync(0xffffffffu, tot, off);
+    }
+    __shared__ float s_mx[kWarps], s_tot[kWarps];
+    if ((threadIdx.x & 31) == 0) {
+        s_mx[threadIdx.x >> 5] = mx;
+        s_tot[threadIdx.x >> 5] = tot;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < kWarps; w++) {
+            mx = fmaxf(mx, s_mx[w]);
+            tot += s_tot[w];
+        }
+        scratch[2 * blockIdx.x] = mx;
+        scratch[2 * blockIdx.x + 1] = tot;
+    }
+}
+
+// one block: the tile partials in a fixed order -> the two result cells
+__global__ void __launch_bounds__(kThreads) k_static_lum_final(int n_tiles, float *__restrict__ scratch)
+{
+    float mx = 0.f, tot = 0.f;
+    for (int b = threadIdx.x; b < n_tiles; b += kThreads) {
+        mx = fmaxf(mx, scratch[2 * b]);
+        tot += scratch[2 * b + 1];
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        mx = fmaxf(mx, __shfl_down_sync(0xffffffffu, mx, off));
+        tot += __shfl_down_sync(0xffffffffu, tot, off);
+    }
+    __shared__ float s_mx[kWarps], s_tot[kWarps];
+    if ((threadIdx.x & 31) == 0) {
+        s_mx[threadIdx.x >> 5] = mx;
+        s_tot[threadIdx.x >> 5] = tot;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < kWarps; w++) {
+            mx = fmaxf(mx, s_mx[w]);
+            tot += s_tot[w];
+        }
+        scratch[2 * PT_STATIC_MAX_TILES] = mx;
+        scratch[2 * PT_STATIC_MAX_TILES + 1] = tot;
+    }
+}
+
+// output_to_file (renderer.h:24-55) with the white point read from the scratch on the device: no host round trip
+__global__ void __launch_bounds__(kThreads) k_static_tonemap(const float4 *__restrict__ accum, int width, int height,
+                                                             float inv_n, float exposure_mul,
+                                                             const float *__restrict__ scratch, uint8_t *__restrict__ rgb)
+{
+    const int npix = width * height;
+    const float white = uncharted2(scratch[2 * PT_STATIC_MAX_TILES]);
+    for (int o = blockIdx.x * kThreads + threadIdx.x; o < npix; o += gridDim.x * kThreads) {
+        int row = o / width, i = o - row * width;
+        int j = height - 1 - row;
+        float4 v = accum[j * width + i];
+        float c[3] = {v.x, v.y, v.z};
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            float x = c[k] * inv_n;
+            x *= exposure_mul;
+            x = clamp01(uncharted2(x) / white);
+            x = 255 * to_srgb(x);
+            rgb[(size_t)o * 3 + k] = (uint8_t)(int)x;
+        }
+    }
+}
+
 } // namespace
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -1069,6 +1169,50 @@ void launch_tonemap(const float4 *accum, int width, int height, float inv_n, flo
     if (blocks > 148 * 8)
         blocks = 148 * 8;
     k_tonemap<<<blocks, kThreads, 0, st>>>(accum, width, height, inv_n, exposure_mul, max_lum, rgb);
+}
+
+// The device address of g_static_scratch on `device` (which must be current).  In host code the array's name is only a
+// host-side stand-in for the symbol: the address a kernel can use comes from cudaGetSymbolAddress, once per device.
+static cudaError_t static_scratch_address(int device, float **out)
+{
+    static std::mutex mu;
+    static float *known[64] = {nullptr};
+    if (device < 0 || device >= 64)
+        return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> g(mu);
+    if (!known[device]) {
+        float *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void **)&p, g_static_scratch);
+        if (e != cudaSuccess)
+            return e;
+        known[device] = p;
+    }
+    *out = known[device];
+    return cudaSuccess;
+}
+
+cudaError_t launch_tonemap_static(int device, const float4 *accum, int width, int height, float inv_n, float exposure_mul,
+                                  uint8_t *rgb, float *h_max_total /* [2] host, or null */, cudaStream_t st)
+{
+    float *scratch = nullptr;
+    cudaError_t e = static_scratch_address(device, &scratch);
+    if (e != cudaSuccess)
+        return e;
+    const int npix = width * height;
+    const int n_tiles = (npix + kStaticTile - 1) / kStaticTile;
+    k_static_lum_partials<<<n_tiles, kThreads, 0, st>>>(accum, npix, inv_n, scratch);
+    k_static_lum_final<<<1, kThreads, 0, st>>>(n_tiles, scratch);
+    int blocks = (npix + kThreads - 1) / kThreads;
+    if (blocks > 148 * 8)
+        blocks = 148 * 8;
+    k_static_tonemap<<<blocks, kThreads, 0, st>>>(accum, width, height, inv_n, exposure_mul, scratch, rgb);
+    e = cudaGetLastError();
+    if (e != cudaSuccess || !h_max_total)
+        return e;
+    e = cudaMemcpyAsync(h_max_total, scratch + 2 * PT_STATIC_MAX_TILES, 2 * sizeof(float), cudaMemcpyDeviceToHost, st);
+    if (e != cudaSuccess)
+        return e;
+    return cudaStreamSynchronize(st);
 }
 
 } // namespace pt

@@ -115,4 +115,13 @@ void launch_pack_rgb(const float4 *accum, int npix, float *rgb, cudaStream_t st)
 void launch_tonemap(const float4 *accum, int width, int height, float inv_n, float exposure_mul, float max_lum,
                     uint8_t *rgb, cudaStream_t st);
 
+// Allocation-free tonemap (b200pt_tonemap_static): luminance reduce + tonemap with the reduce's scratch in a file-scope
+// __device__ array of kernels.cu.  One tile of PT_STATIC_TILE pixels per partial, at most PT_STATIC_MAX_TILES tiles.
+#define PT_STATIC_TILE 1024
+#define PT_STATIC_MAX_TILES 16384
+#define PT_STATIC_MAX_PIXELS (PT_STATIC_TILE * PT_STATIC_MAX_TILES) /* 16 777 216: twice a 3840 x 2160 film */
+#define PT_STATIC_SCRATCH_FLOATS (2 * PT_STATIC_MAX_TILES + 64)
+cudaError_t launch_tonemap_static(int device, const float4 *accum, int width, int height, float inv_n, float exposure_mul,
+                                  uint8_t *rgb, float *h_max_total /* [2] host, or null */, cudaStream_t st);
+
 } // namespace pt
