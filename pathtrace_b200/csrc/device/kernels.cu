@@ -251,6 +251,7 @@ __global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView
         mr.xi = -1.f;
         if (live) {
             slot = q_in ? q_in[i] : i;
+            PT_CHECK(slot >= 0 && slot < wf.capacity);
             float4 ro = wf.ray[2 * slot], rd = wf.ray[2 * slot + 1];
             mr.key = make_key(rp, wf, slot, sample_base);
             mr.stage = stage_word(bounce, RNG_EXT_MEDIUM, 0);
@@ -277,6 +278,7 @@ __global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView
         block_reserve<SK_COUNT, kExtThreads / 32>(mask, kind_counter, pos);
         if (mask) {
             int kind = __ffs(mask) - 1;
+            PT_CHECK(pos[kind] >= 0 && pos[kind] < wf.capacity);
             wf.q_kind[kind][pos[kind]] = slot;
         }
     }
@@ -304,6 +306,7 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
         uint32_t key_nee = 0, key_ext = 0;
         if (i < n) {
             slot = q_in[i];
+            PT_CHECK(slot >= 0 && slot < wf.capacity);
             float4 ro = wf.ray[2 * slot], rd = wf.ray[2 * slot + 1], bt = wf.thr[2 * slot];
             if (kind == SK_MISS) {
                 V3 add = shade_miss(s, xyz(rd), xyz(bt));
@@ -379,6 +382,8 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
         }
         int pos[2];
         block_reserve<2>(mask, counter, pos);
+        PT_CHECK(!(mask & 1u) || (pos[0] >= 0 && pos[0] < wf.capacity));
+        PT_CHECK(!(mask & 2u) || (pos[1] >= 0 && pos[1] < wf.capacity));
         if (mask & 1u) {
             q_nee_out[pos[0]] = slot;
             if (sorted)
@@ -442,7 +447,9 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
             k = (int)(e - (unsigned)q * (unsigned)L);
         }
         if (e < n && k < L) {
+            PT_CHECK(q >= 0 && q < wf.counters[bounce * CNT_ROW + CNT_NEE] && q < wf.capacity);
             slot = wf.q_nee[q];
+            PT_CHECK(slot >= 0 && slot < wf.capacity);
             float4 hp = wf.hit[2 * slot], hn = wf.hit[2 * slot + 1], w = wf.acc[2 * slot];
             RngKey key = make_key(rp, wf, slot, sample_base);
             nrays++;
@@ -526,6 +533,7 @@ __global__ void __launch_bounds__(kThreads) k_sort_hist(const uint32_t *__restri
         const bool live = i < n;
         const uint32_t key = live ? keys[i] : 0xffffffffu;
         const unsigned peers = __match_any_sync(0xffffffffu, key);
+        PT_CHECK(!live || key < (uint32_t)PT_SORT_BUCKETS);
         if (live && lane == __ffs(peers) - 1)
             atomicAdd(hist + key, (uint32_t)__popc(peers));
     }
@@ -618,6 +626,7 @@ __global__ void __launch_bounds__(kThreads) k_sort_scatter(const uint32_t *__res
         if (live && lane == leader)
             first = atomicAdd(hist + key, (uint32_t)__popc(peers)) + s_chunk[key / PT_SORT_CHUNK];
         first = __shfl_sync(0xffffffffu, first, leader);
+        PT_CHECK(!live || first + (uint32_t)__popc(peers & ((1u << lane) - 1u)) < (uint32_t)n);
         if (live)
             dst[first + __popc(peers & ((1u << lane) - 1u))] = raw[i];
     }
