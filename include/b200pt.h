@@ -207,6 +207,9 @@ int b200pt_scene_create(const b200pt_scene_desc *desc, int32_t device, b200pt_sc
 int b200pt_scene_get_desc(const b200pt_scene *scene, b200pt_scene_desc *out);
 /* Statistics of the tree the kernels walk (4 children per node): n_nodes, depth, and the scene bounds. */
 int b200pt_scene_bvh_info(const b200pt_scene *scene, int32_t *n_nodes, int32_t *max_depth, float bounds[6]);
+/* Drops the caller's reference.  A scene that still has renders stays alive until the last of them is destroyed (the
+ * reference news everything and never frees, main.cpp:108-168; a binding whose garbage collector finalizes the scene object
+ * before the renderer object must not crash). */
 void b200pt_scene_destroy(b200pt_scene *scene);
 
 /* ---- closest-hit queries (parity entry point) ------------------------------------------- */

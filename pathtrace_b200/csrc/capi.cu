@@ -290,6 +290,10 @@ struct b200pt_scene {
     uint32_t shade_kinds = 1u << pt::SK_MISS; // shade queues that can ever be non-empty for this scene
     std::mutex replica_mu;
     std::map<int, std::unique_ptr<b200pt_scene>> replicas; // device -> upload of the same host scene (multi-GPU renders)
+    // One reference for the caller's handle and one per live render: b200pt_scene_destroy on a scene that still has renders
+    // only drops the caller's reference, the memory goes when the last render is destroyed (a garbage collector may well
+    // finalize the scene object first).
+    std::atomic<int> refs{1};
 
     b200pt_scene() : host(std::make_shared<SceneHost>()), flat(host->flat), packed(host->packed) {}
     explicit b200pt_scene(std::shared_ptr<SceneHost> h) : host(std::move(h)), flat(host->flat), packed(host->packed) {}
@@ -309,6 +313,12 @@ struct b200pt_scene {
 };
 
 namespace {
+
+void scene_unref(b200pt_scene *sc)
+{
+    if (sc && sc->refs.fetch_sub(1) == 1)
+        delete sc;
+}
 
 void upload_scene(b200pt_scene &sc, bool pack = true)
 {
@@ -748,7 +758,10 @@ struct b200pt_render {
         while (shards.size() > 1)
             shards.pop_back();
         shards.clear();
+        if (scene_ref_held)
+            scene_unref(scene); // may be the last reference (the caller destroyed the scene handle first)
     }
+    bool scene_ref_held = false;
 };
 
 namespace {
@@ -1077,7 +1090,7 @@ int b200pt_scene_bvh_info(const b200pt_scene *scene, int32_t *n_nodes, int32_t *
     return B200PT_OK;
 }
 
-void b200pt_scene_destroy(b200pt_scene *scene) { delete scene; }
+void b200pt_scene_destroy(b200pt_scene *scene) { scene_unref(scene); }
 
 int b200pt_trace_batch_device(b200pt_scene *scene, const void *d_rays, size_t n, const void *d_medium_xi, void *d_hits,
                               int32_t repeat, float *ms)
@@ -1238,6 +1251,8 @@ int b200pt_render_start(b200pt_scene *scene, const b200pt_config *config, b200pt
         }
         std::unique_ptr<b200pt_render> r(new b200pt_render);
         r->scene = scene;
+        scene->refs.fetch_add(1);
+        r->scene_ref_held = true;
         r->cfg = c;
         r->async = c.async_render != 0;
         const int n = (int)devs.size();

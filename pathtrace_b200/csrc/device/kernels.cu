@@ -307,12 +307,26 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
         if (i < n) {
             slot = q_in[i];
             PT_CHECK(slot >= 0 && slot < wf.capacity);
-            float4 ro = wf.ray[2 * slot], rd = wf.ray[2 * slot + 1], bt = wf.thr[2 * slot];
             if (kind == SK_MISS) {
-                V3 add = shade_miss(s, xyz(rd), xyz(bt));
-                const float4 acc = wf.acc[2 * slot + 1];
-                wf.acc[2 * slot + 1] = make_float4(acc.x + add.x, acc.y + add.y, acc.z + add.z, 0.f);
-            } else {
+                // integrator.h:325-335: sum += beta * background.  A constant background (every shipped scene) needs
+                // no ray direction, and a zero product -- a black sky -- leaves the sum alone: one 32-byte sector per miss
+                // instead of five.  (x + 0 == x for every x, NaN included; a NaN or infinite beta still gives a NaN product
+                // and is added, as in the reference.)
+                const float4 bt = wf.thr[2 * slot];
+                const b200pt_texture &bg = s.tex[s.background];
+                V3 add;
+                if (bg.kind == B200PT_TEX_CONSTANT)
+                    add = xyz(bt) * v3(bg.color[0], bg.color[1], bg.color[2]);
+                else
+                    add = shade_miss(s, xyz(wf.ray[2 * slot + 1]), xyz(bt));
+                if (add.x != 0.f || add.y != 0.f || add.z != 0.f) {
+                    const float4 acc = wf.acc[2 * slot + 1];
+                    wf.acc[2 * slot + 1] = make_float4(acc.x + add.x, acc.y + add.y, acc.z + add.z, 0.f);
+                }
+                continue; // a miss never appends (every thread of the block takes the `continue` below)
+            }
+            float4 ro = wf.ray[2 * slot], rd = wf.ray[2 * slot + 1], bt = wf.thr[2 * slot];
+            {
                 float4 hp = wf.hit[2 * slot], hn = wf.hit[2 * slot + 1];
                 PathVertexIn in;
                 in.o = xyz(ro);

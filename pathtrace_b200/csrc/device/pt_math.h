@@ -44,7 +44,9 @@ PT_HD V3 operator*(V3 a, float t) { return v3(t * a.x, t * a.y, t * a.z); }
 // b, so those lanes skip the division (ncu: 16 % of k_nee's instructions were that subroutine).
 PT_HD float fdiv(float a, float b)
 {
-#if defined(__CUDA_ARCH__)
+#if defined(__CUDA_ARCH__) && defined(PT_FAST_DIV)
+    return __fdividef(a, b); // A/B: approximate division (2 ulp), no FCHK slow path
+#elif defined(__CUDA_ARCH__)
     // branch-free: such a lane divides b by b (fast path) and the quotient is replaced by the signed zero
     const bool zero = a == 0.f && b == b && b != 0.f;
     const float q = (zero ? b : a) / b;

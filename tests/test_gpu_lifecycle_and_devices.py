@@ -81,6 +81,24 @@ def test_async_render_start_returns_and_poll_reports():
     assert np.array_equal(img, img_ref) and mx == mx_ref
 
 
+def test_scene_destroyed_before_its_render():
+    """A garbage collector may finalize the Scene object before the Wavefront that renders it (seen when a failing test left
+    both to the cyclic collector): b200pt_scene_destroy then only drops the caller's reference, the render keeps working and
+    its destruction releases the scene."""
+    import pathtrace_b200 as pt
+    cfg = _cfg("book2_final", 96, 54, 4)
+    scene, r, _ = _paced("book2_final", cfg)
+    before = r.framebuffer
+    scene.close()                       # the handle is gone ...
+    assert np.array_equal(r.framebuffer, before)   # ... the render is not
+    img, mx, _ = r.tonemap()
+    assert mx > 0 and img.mean() > 0
+    r.close()
+    # and a render destroyed twice / a scene closed twice are no-ops on the Python side
+    r.close()
+    scene.close()
+
+
 @pytest.mark.parametrize("n_dev,async_render,no_peer", [(2, 0, False), (3, 1, False), (2, 1, True)])
 def test_devices_inside_the_library(monkeypatch, n_dev, async_render, no_peer):
     """device_count shards behind ONE handle: the combined film equals the sum of the shards rendered one by one
