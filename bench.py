@@ -320,7 +320,7 @@ def ours_arm(args):
     scene = pt.Scene.from_json(scene_json, w, h, device=local)
     first_r, count_r = ptd.shard_samples(spp_step, world, rank)
     base = pt.Config.from_json(cfg_json).replace(device=local)
-    target_slots = int(os.environ.get("B200PT_BATCH_SLOTS", "0")) or (32 << 20)
+    target_slots = int(os.environ.get("B200PT_BATCH_SLOTS", "0")) or (128 << 20)  # the library's default (capi.cu)
     batch = pick_batch(count_r, max(1, target_slots // npix))
     batches_per_step = count_r // batch
     cfg = base.replace(samples=(W + K) * count_r, sample_offset=(W + K) * first_r, batch_samples=batch)

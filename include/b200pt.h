@@ -143,7 +143,7 @@ typedef struct b200pt_config {
     uint64_t seed;          /* Philox key */
     int64_t sample_offset;  /* first global sample index rendered by this handle (spp sharding) */
     int32_t device;         /* CUDA device ordinal */
-    int32_t batch_samples;  /* samples per pixel per wavefront batch; 0 = auto (about 32 Mi paths in flight, ~6.5 GB of state;
+    int32_t batch_samples;  /* samples per pixel per wavefront batch; 0 = auto (up to 128 Mi paths in flight, ~24 GB of state;
                                the environment variable B200PT_BATCH_SLOTS overrides that target) */
     float stats_clamp;      /* >0: also accumulate per-pixel sum / sum of squares of the per-sample
                                radiance clamped to [-stats_clamp, stats_clamp] (parity statistics; a Perlin albedo can be
@@ -338,7 +338,7 @@ void b200pt_render_destroy(b200pt_render *render);
 /* Device and pinned-host blocks of destroyed handles are kept for reuse by later handles (the reference `new`s
  * everything once per process and never frees, main.cpp:108-168; a library that is called once per frame must not pay
  * cudaMalloc for 1.3 GB of wavefront state every time).  This releases them.  Env B200PT_CACHE_MB caps the cache
- * (default 8192, 0 = off). */
+ * (default 49152, 0 = off). */
 void b200pt_trim_cache(void);
 
 #ifdef __cplusplus

@@ -68,7 +68,8 @@ template <typename F> int guarded(F &&f)
 // Device and pinned-host blocks of destroyed handles are kept for the next handle that asks for the same size: a
 // render allocates ~1.3 GB of wavefront state in 20 blocks, and cudaMalloc/cudaFree of those cost more than
 // rendering a few samples per pixel.  Blocks enter the cache only after the owning stream has been synchronised.
-// B200PT_CACHE_MB caps the cached device bytes (default 8192; 0 disables); b200pt_trim_cache() empties it.
+// B200PT_CACHE_MB caps the cached device bytes (default 49152 = two full-size wavefront batches; 0 disables);
+// b200pt_trim_cache() empties it.
 class BlockCache {
   public:
     void *dev_get(int device, size_t bytes)
@@ -156,7 +157,7 @@ class BlockCache {
     {
         static const size_t c = [] {
             const char *e = std::getenv("B200PT_CACHE_MB");
-            return (size_t)(e ? std::max(0ll, atoll(e)) : 8192ll) << 20;
+            return (size_t)(e ? std::max(0ll, atoll(e)) : 49152ll) << 20;
         }();
         return c;
     }
@@ -583,7 +584,10 @@ std::unique_ptr<Shard> make_shard(b200pt_scene *scene, const b200pt_config &c)
         if (npix > (1ll << 30))
             throw std::runtime_error("film too large");
         // batch sizing: enough paths in flight to fill 148 SMs many times over, small enough to stay a few GB
-        long long target_slots = 32ll << 20;
+        // 128 Mi slots (~24 GB of path state and queues): measured on book2_final 4K, 32 / 64 / 128 Mi slots give
+        // 865 / 888 / 900 Mpaths/s -- the launches of the late bounces are short, and a larger batch makes their ramp-up and
+        // tail weigh less; the memory is there (180 GB)
+        long long target_slots = 128ll << 20;
         if (const char *e = std::getenv("B200PT_BATCH_SLOTS")) // tuning aid: paths in flight per wavefront batch
             if (std::atoll(e) > 0)
                 target_slots = std::atoll(e);

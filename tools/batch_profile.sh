@@ -19,5 +19,5 @@ PY
 )}
 echo "launches per batch: $N"
 ncu --metrics $M --clock-control none -s $N -c $N --csv --log-file $OUT/${TAG}_batch_$SCENE.csv $CMD > $OUT/ncu_batch_$SCENE.log 2>&1
-python tools/batch_table.py $SCENE $OUT/${TAG}_batch_$SCENE.csv > $OUT/${TAG}_batch_$SCENE.txt
+python tools/batch_table.py $SCENE $OUT/${TAG}_batch_$SCENE.csv $OUT/${TAG}_batch_$SCENE.json > $OUT/${TAG}_batch_$SCENE.txt
 tail -40 $OUT/${TAG}_batch_$SCENE.txt

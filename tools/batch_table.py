@@ -7,6 +7,7 @@ import re
 import sys
 
 scene, path = sys.argv[1:3]
+json_out = sys.argv[3] if len(sys.argv) > 3 else None
 with open(path) as f:
     lines = [l for l in f if not l.startswith("==")]
 rows = collections.OrderedDict()
@@ -41,14 +42,26 @@ for i, (k, d) in enumerate(rows.items()):
     inst = d.get("smsp__inst_executed.sum", 0.0)
     print(f"{i:4d} {name:34s} {t:9.1f} {lanes:8.2f} {d.get('smsp__issue_active.avg.pct_of_peak_sustained_active', 0):7.1f} "
           f"{d.get('lts__t_sector_hit_rate.pct', 0):7.1f} {inst / 1e6:10.1f} {by / 1e6:9.1f} {by / max(t, 1e-9) / 1e3:7.0f}")
-    a = agg.setdefault(re.sub(r"<.*", "", name), [0, 0.0, 0.0, 0.0, 0.0])
+    a = agg.setdefault(re.sub(r"<.*", "", name), [0, 0.0, 0.0, 0.0, 0.0, 0.0])
     a[0] += 1
     a[1] += t
     a[2] += by
     a[3] += inst
     a[4] += inst * lanes
+    a[5] += t * d.get("smsp__issue_active.avg.pct_of_peak_sustained_active", 0.0)
 tot = sum(a[1] for a in agg.values())
 print(f"\n{'kernel':20s} {'launches':>8s} {'total_us':>10s} {'share':>6s} {'dramMB':>9s} {'GB/s':>7s} {'lanes/32':>8s}")
 for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     print(f"{k:20s} {a[0]:8d} {a[1]:10.1f} {a[1] / tot:6.3f} {a[2] / 1e6:9.1f} {a[2] / max(a[1], 1e-9) / 1e3:7.0f} {a[4] / max(a[3], 1e-9):8.2f}")
 print(f"{'TOTAL':20s} {sum(a[0] for a in agg.values()):8d} {tot:10.1f}")
+if json_out:
+    import json
+    out = {}
+    for k, a in agg.items():
+        name = k.split("::")[-1]
+        out[name] = {"launches": a[0], "total_us": round(a[1], 1), "share_of_batch": round(a[1] / tot, 4),
+                     "dram_bytes_per_launch": round(a[2] / a[0]), "dram_gbs": round(a[2] / max(a[1], 1e-9) / 1e3, 1),
+                     "issue_active_pct": round(a[5] / max(a[1], 1e-9), 2),      # time-weighted over the launches
+                     "lanes_per_warp_inst": round(a[4] / max(a[3], 1e-9), 2)}  # instruction-weighted
+    with open(json_out, "w") as f:
+        json.dump(out, f, indent=1)
