@@ -33,44 +33,66 @@ def _cfg(scene, w, h, spp, **kw):
     return pt.default_config_dict(width=w, height=h, samples=spp, scene=scene_path(scene), **kw)
 
 
-def _close(a, b, what):
-    """Sample sums agree up to libm ulps amplified through a few bounces; a plumbing error shows up as O(1)."""
+def _close(a, b, what, frac_limit=5e-3, total_limit=1e-3, level="loose"):
+    """Sample sums agree up to libm ulps (CUDA's sinf / cosf / logf / powf vs glibc's) amplified through a few bounces; a
+    plumbing error -- a lost queue slot, a sample added twice -- shows up as O(1) on the pixels it touches.  Limits are a
+    few times what the cases measure (gpurun_out/parity/close_stats.jsonl).  level:
+      "bit"    no libm call on the path (direct lighting from rect lights, RecursivePT's products): bit-equal sums
+      "tight"  trig / powf ulps only, no decision can flip at these sizes: every pixel within 1e-4 relative (measured <= 6e-6)
+      "loose"  media (logf decides whether a scatter event happens), Russian roulette on long paths, sphere lights: a flipped
+               decision changes a whole sample -- at most 5e-3 of the pixels beyond 1e-3 (measured 1.6e-3), totals 1e-3."""
     scale = np.maximum(np.abs(b), 1e-3 * max(1.0, float(np.abs(b).max())))
     rel = np.abs(a - b) / scale
     frac_bad = float((rel > 1e-3).mean())
-    assert frac_bad < 1e-2, (what, frac_bad, float(rel.max()))
     tot_a, tot_b = float(a.astype(np.float64).sum()), float(b.astype(np.float64).sum())
-    assert abs(tot_a - tot_b) <= 1e-2 * abs(tot_b) + 1e-6, (what, tot_a, tot_b)
+    try:
+        os.makedirs(os.path.join(ROOT, "gpurun_out", "parity"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", "parity", "close_stats.jsonl"), "a") as f:
+            f.write(json.dumps({"what": str(what), "frac_gt_1e-3": frac_bad, "rel_max": float(rel.max()),
+                                "bit_equal": bool(np.array_equal(a, b)),
+                                "total_rel": abs(tot_a - tot_b) / max(abs(tot_b), 1e-30)}) + "\n")
+    except OSError:
+        pass
+    if level == "bit":
+        assert np.array_equal(a, b), (what, frac_bad, float(rel.max()))
+    if level == "tight":
+        assert float(rel.max()) <= 1e-4, (what, float(rel.max()))
+    assert frac_bad < frac_limit, (what, frac_bad, float(rel.max()))
+    assert abs(tot_a - tot_b) <= total_limit * abs(tot_b) + 1e-6, (what, tot_a, tot_b)
 
 
 CASES = [
-    ("three_orbs", dict()),
-    ("cornell_box", dict()),
-    ("cornell_box_small_lights", dict(light_samples=3)),
-    ("cornell_box_with_volume", dict()),
-    ("cornell_box_with_volume2", dict(russian_roulette=False, max_bounces=4)),
-    ("light_test", dict(light_samples=1)),
-    ("book2_final", dict()),
-    ("cornell_box", dict(integrator_type="recursive path tracing")),
-    ("three_orbs", dict(integrator_type="recursive path tracing", max_bounces=5)),
-    ("cornell_box", dict(only_direct_illumination=True)),
-    ("cornell_box", dict(max_bounces=1)),
-    ("cornell_box_image_textures", dict()),
-    ("cornell_box_image_textures", dict(integrator_type="recursive path tracing", max_bounces=3)),
+    ("three_orbs", dict(), "tight"),
+    ("cornell_box", dict(), "tight"),
+    ("cornell_box_small_lights", dict(light_samples=3), "tight"),
+    ("cornell_box_with_volume", dict(), "tight"),
+    ("cornell_box_with_volume2", dict(russian_roulette=False, max_bounces=4), "tight"),
+    ("light_test", dict(light_samples=1), "loose"),
+    ("book2_final", dict(), "loose"),
+    ("cornell_box", dict(integrator_type="recursive path tracing"), "bit"),
+    ("three_orbs", dict(integrator_type="recursive path tracing", max_bounces=5), "bit"),
+    ("cornell_box", dict(only_direct_illumination=True), "bit"),
+    ("cornell_box", dict(max_bounces=1), "bit"),
+    ("cornell_box", dict(russian_roulette=False, max_bounces=3), "tight"),
+    ("cornell_box_image_textures", dict(), "tight"),
+    ("cornell_box_image_textures", dict(integrator_type="recursive path tracing", max_bounces=3), "bit"),
 ]
 
 
-@pytest.mark.parametrize("scene,over", CASES)
-def test_render_matches_cpu_restatement(scene, over):
+@pytest.mark.parametrize("scene,over,level", CASES)
+def test_render_matches_cpu_restatement(scene, over, level):
     w, h, spp = 48, 40, 6
     cfgd = _cfg(scene, w, h, spp, **over)
     r, rep = _render(cfgd, batch_samples=4)  # 2 batches: 4 + 2 samples
     fb = r.framebuffer
     oracle = PortOracle.from_file(scene_path(scene), w, h)
     ref = oracle.render(make_cconfig(cfgd), stats=False)
-    _close(fb, ref["sums"], scene)
-    # ray accounting: a differing libm ulp can flip a Russian-roulette or medium decision on a handful of paths
+    _close(fb, ref["sums"], scene, level=level)
+    # ray accounting: exact where no decision can flip; else a differing libm ulp can flip a Russian-roulette or medium
+    # decision on a handful of paths
     for k in ("rays_extension", "rays_shadow", "rays_reference"):
+        if level == "bit":
+            assert rep[k] == ref[k], (k, rep[k], ref[k])
         assert abs(rep[k] - ref[k]) <= 2e-3 * ref[k] + 8, (k, rep[k], ref[k])
     assert rep["camera_rays"] == w * h * spp
 
