@@ -136,16 +136,46 @@ def run_reference_once(cfgd, spp, threads, block=32, timeout=3000):
             "mpaths_per_s": paths / secs * 1e-6, "mrays_per_s": rays / secs * 1e-6}
 
 
+def usable_threads():
+    """Host threads this process may run on (respects cpusets / affinity; os.cpu_count() reports the whole machine)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def with_film(cfgd, w, h):
+    return dict(cfgd, film=dict(cfgd["film"], width=int(w), height=int(h)))
+
+
 def cpu_sample(cfgd, threads, target_seconds):
-    """One bounded run of the reference on the bench film: a 1-spp probe calibrates the sample count for a run of about
-    `target_seconds`; when the probe alone is already that long (the 4K film) the probe IS the sample."""
-    probe = run_reference_once(cfgd, 1, threads)
-    if probe["wall_seconds"] >= 0.6 * target_seconds:
-        return 1, probe
-    rate = probe["paths"] / max(probe["wall_seconds"], 0.25)
-    npix = cfgd["film"]["width"] * cfgd["film"]["height"]
-    spp = max(1, min(64, int(round(rate * target_seconds / npix))))
-    return spp, run_reference_once(cfgd, spp, threads)
+    """One BOUNDED run of the reference on the bench scene, sized for about `target_seconds` of wall clock.  The rates the
+    reference prints (paths / s, rays / s) do not depend on the film size or the sample count, so the sample is the same
+    scene, camera and settings on a film scaled down (same aspect) until 1 spp fits the budget -- the full film at several
+    spp when that fits too.  Calibrated on a 1/8-size film; every run has a hard timeout, and if the sized run does not
+    finish the probe itself is the sample.  Returns (description, run)."""
+    w, h = cfgd["film"]["width"], cfgd["film"]["height"]
+    pw, ph = max(32, w // 8), max(18, h // 8)
+    try:
+        probe = run_reference_once(with_film(cfgd, pw, ph), 1, threads, timeout=180)
+    except subprocess.TimeoutExpired:  # a pathologically slow host: a thumbnail, or give up (the caller reports it)
+        pw, ph = 64, max(18, 64 * h // max(w, 1))
+        probe = run_reference_once(with_film(cfgd, pw, ph), 1, threads, timeout=300)
+        return f"{pw}x{ph} at 1 spp (the 1/8-size probe exceeded its time limit)", probe
+    rate = probe["paths"] / max(probe["wall_seconds"], 0.25)  # paths per second of wall clock, scene build included
+    budget = rate * target_seconds
+    if budget >= w * h:
+        sw, sh, spp = w, h, max(1, min(64, int(budget // (w * h))))
+    else:
+        f = max((budget / float(w * h)) ** 0.5, pw / float(w))
+        sw, sh, spp = max(pw, int(w * f)), max(ph, int(h * f)), 1
+    desc = f"{sw}x{sh} at {spp} spp"
+    if (sw, sh, spp) == (pw, ph, 1):
+        return desc, probe
+    try:
+        return desc, run_reference_once(with_film(cfgd, sw, sh), spp, threads, timeout=max(60.0, 5.0 * target_seconds))
+    except subprocess.TimeoutExpired:
+        return f"{pw}x{ph} at 1 spp (the sized run of {desc} exceeded its time limit)", probe
 
 
 def workload_name(args, w, h):
@@ -160,26 +190,44 @@ def reference_arm(args):
     if rank != 0:
         return 0
     cfgd = config_dict(args)
-    threads = os.cpu_count() or 1
+    threads = usable_threads()
     w, h = cfgd["film"]["width"], cfgd["film"]["height"]
-    probe = run_reference_once(cfgd, 1, threads)  # doubles as the warm-up run
-    per_spp = max(probe["wall_seconds"], 0.25)
-    spp = max(1, min(64, int(10.0 / per_spp)))  # a step of about 10 s, at least 1 spp of the whole film
-    budget = 150.0  # seconds of timed runs
-    steps = max(1, min(args.steps, int(budget / (per_spp * spp))))
+    t_arm = time.perf_counter()
+    try:
+        desc, first = cpu_sample(cfgd, threads, 10.0)  # calibration + the first sample; doubles as the warm-up run
+    except Exception as e:  # noqa: BLE001 -- the arm must end with a line and exit 0 whatever the host does
+        print(json.dumps({"impl": "reference", "unavailable": f"reference CPU run failed or timed out: {e}"[:300]}), flush=True)
+        return 0
+    per_step = max(first["wall_seconds"], 0.5)
+    budget = 150.0  # seconds of timed runs, whatever --steps asks for
+    steps = max(1, min(args.steps, int(budget / per_step)))
     warm = 1
-    runs = [run_reference_once(cfgd, spp, threads) for _ in range(steps)]
+    m = re.match(r"(\d+)x(\d+) at (\d+) spp", desc)
+    sw, sh, spp = int(m.group(1)), int(m.group(2)), int(m.group(3))
+    runs = []
+    for _ in range(steps):
+        if runs and time.perf_counter() - t_arm > 240.0:
+            break  # never let the arm run away
+        try:
+            runs.append(run_reference_once(with_film(cfgd, sw, sh), spp, threads, timeout=max(60.0, 6.0 * per_step)))
+        except subprocess.TimeoutExpired:
+            break
+    if not runs:
+        runs = [first]
+    steps = len(runs)
     paths = sum(r["paths"] for r in runs)
     secs = sum(r["seconds"] for r in runs)
     rays = sum(r["rays"] for r in runs)
     value = paths / secs * 1e-6
-    sample = (f"{args.scene} {w}x{h} at {spp} spp per step x {steps} steps (bounded: --steps {args.steps} asked), tiled "
-              f"32x32 blocks, {threads} threads, unmodified reference main(); rates as it prints them (renderer.h:705-706)")
+    sample = (f"{args.scene}, film {desc} per step x {steps} steps (bounded sample of the {w}x{h} workload: the same scene, "
+              f"camera and settings, rates do not depend on film size; --steps {args.steps} asked), tiled 32x32 blocks, "
+              f"{threads} threads, unmodified reference main(); rates as it prints them (renderer.h:705-706)")
     line = {
         "impl": "reference", "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": secs / steps * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args, w, h), "spp_per_step": spp, "steps_requested": args.steps},
+        "config": {"workload": workload_name(args, w, h), "sample_film": f"{sw}x{sh}", "spp_per_step": spp,
+                   "steps_requested": args.steps},
         "mrays_per_s": rays / secs * 1e-6, "rays_per_path": rays / paths,
         "cpu_baseline": {"value": value, "unit": "Mpaths/s", "cores": threads, "kind": "reference", "sample": sample},
         "e2e": {"value": value, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -235,9 +283,10 @@ def traversal_roofline(prof_time, prof_count, peaks, scene_name, small_scene):
     kernels = {"k_extend": one("extend", "ext"), "k_nee": one("nee", "nee")}
     k = kernels["k_" + top]
     frac = k["frac_of_hbm"]
-    valid = (not small_scene) and frac <= 1.2
+    valid = (not small_scene) and frac <= 1.0
     why = ("scene records are staged in shared memory: the 8d byte count never comes from HBM" if small_scene else
-           ("frac > 1.2: served from L1/L2, not HBM" if frac > 1.2 else
+           ("frac > 1: the node / instance records are served from L1/L2 (the scene is 1.6 MB), not HBM -- the SURVEY 8d "
+            "byte model is not a bound here; see issue_bound and traffic (measured DRAM bytes)" if frac > 1.0 else
             "scene is L2-resident (1.6 MB): an upper bound on fetch traffic, not on DRAM traffic"))
     return {
         "bound": "hbm", "kernel": "k_" + top, "achieved": k["algorithmic_gbs"], "peak": peak, "unit": "GB/s",
@@ -439,17 +488,17 @@ def main():
     roof = traversal_roofline(prof_time, prof_count, load_peaks(), args.scene, res["small_scene"])
     cpu = None
     if world == 1 and not args.no_cpu_baseline and os.path.exists(REF_DRIVER):
-        threads = os.cpu_count() or 1
+        threads = usable_threads()
         try:
-            spp, run = cpu_sample(res["cfgd"], threads, args.cpu_seconds)
+            desc, run = cpu_sample(res["cfgd"], threads, args.cpu_seconds)
             cpu = {"value": run["mpaths_per_s"], "unit": "Mpaths/s", "cores": threads, "kind": "reference",
                    "mrays_per_s": run["mrays_per_s"], "seconds": run["seconds"],
-                   "sample": f"{args.scene} {res['w']}x{res['h']} at {spp} spp, unmodified reference main() "
+                   "sample": f"{args.scene}, film {desc} (bounded sample of the {res['w']}x{res['h']} workload: same scene, "
+                             f"camera and settings; rates do not depend on film size), unmodified reference main() "
                              f"(tiled, 32x32 blocks, {threads} threads)"}
             if args.cpu_one_thread:  # the deterministic single-thread rate (no RNG race), on a reduced film
-                one = dict(res["cfgd"], film=dict(res["cfgd"]["film"], width=max(32, res["w"] // 8),
-                                                  height=max(18, res["h"] // 8)))
-                r1 = run_reference_once(one, 1, 1)
+                one = with_film(res["cfgd"], max(32, res["w"] // 16), max(18, res["h"] // 16))
+                r1 = run_reference_once(one, 1, 1, timeout=300)
                 cpu["one_thread"] = {"value": r1["mpaths_per_s"], "mrays_per_s": r1["mrays_per_s"],
                                      "sample": f"{one['film']['width']}x{one['film']['height']} at 1 spp, 1 thread"}
         except Exception as e:  # the baseline is reported, never required

@@ -538,8 +538,10 @@ void enqueue_batch(Shard &r)
         });
         if (r.wf.sort_on) {
             const bool more = b + 1 < n_bounces;
-            launch_class(r, B200PT_K_SORT, (nee ? 3 : 0) + (more ? 3 : 0), [&] {
-                if (nee)
+            // (the camera vertices' NEE queue is in pixel order already, but sorting it too is worth it: 901 vs 894 Mpaths/s)
+            const bool nee_sorted = nee;
+            launch_class(r, B200PT_K_SORT, (nee_sorted ? 3 : 0) + (more ? 3 : 0), [&] {
+                if (nee_sorted)
                     pt::launch_sort_queue(r.wf, r.wf.key_nee, r.wf.q_raw_nee, r.wf.q_nee, b * pt::CNT_ROW + pt::CNT_NEE, r.lc, st);
                 if (more)
                     pt::launch_sort_queue(r.wf, r.wf.key_ext, r.wf.q_raw_ext, r.wf.q_ext[(b + 1) & 1],
