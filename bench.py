@@ -114,7 +114,12 @@ REF_DRIVER = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
 def run_reference_once(cfgd, spp, threads, block=32, timeout=3000):
     """One run of the UNMODIFIED reference main() (main.cpp:108-168 via oracle/_ref/ref_driver main): tiled
     renderer, `threads` workers, block x block tiles so that tiles >= threads.  Returns the two rates
-    the program prints itself (renderer.h:703-706).  Its clock has the 0.5 s granularity of its polling loop."""
+    the program prints itself (renderer.h:703-706).  Its clock has the 0.5 s granularity of its polling loop.
+
+    The reference never joins its worker threads (main.cpp:153-167) and, with 16 of them, was seen not to EXIT after
+    finalize() had printed everything (reproduced here: rates printed after 2 s, process still there after 120 s).  So the
+    harness does not wait for the process: it reads the output as it appears and stops the process once the last line
+    finalize() prints ("max lum", renderer.h:722) is there.  Raises subprocess.TimeoutExpired if that takes > `timeout` s."""
     if not os.path.exists(REF_DRIVER):
         raise FileNotFoundError(REF_DRIVER + " missing: run __graft_entry__.build() where /root/reference is mounted")
     with tempfile.TemporaryDirectory() as d:
@@ -124,9 +129,31 @@ def run_reference_once(cfgd, spp, threads, block=32, timeout=3000):
                  traced_paths_2d_output_path=os.path.join(d, "p2.txt"))
         with open(os.path.join(d, "config.json"), "w") as f:
             json.dump(c, f)
+        log = os.path.join(d, "stdout.txt")
         t0 = time.perf_counter()
-        out = subprocess.run([REF_DRIVER, "main"], cwd=d, capture_output=True, text=True, timeout=timeout).stdout
-        wall = time.perf_counter() - t0
+        with open(log, "wb") as sink:
+            proc = subprocess.Popen([REF_DRIVER, "main"], cwd=d, stdout=sink, stderr=subprocess.DEVNULL)
+        out, wall = "", None
+        try:
+            while True:
+                with open(log, "r", errors="replace") as f:
+                    out = f.read()
+                if "max lum" in out or proc.poll() is not None:
+                    wall = time.perf_counter() - t0
+                    break
+                if time.perf_counter() - t0 > timeout:
+                    raise subprocess.TimeoutExpired([REF_DRIVER, "main"], timeout)
+                time.sleep(0.05)
+            try:
+                proc.wait(timeout=2.0)  # a well-behaved exit; else stop it -- everything we need has been printed
+            except subprocess.TimeoutExpired:
+                pass
+        finally:
+            if proc.poll() is None:
+                proc.kill()
+                proc.wait()
+        with open(log, "r", errors="replace") as f:
+            out = f.read()
     m1 = re.search(r"computed (\d+) camera rays in ([0-9.eE+-]+)s", out)
     m2 = re.search(r"computed (\d+) rays, at ([0-9.eE+-]+) rays per second", out)
     if not m1 or not m2:
@@ -149,33 +176,46 @@ def with_film(cfgd, w, h):
 
 
 def cpu_sample(cfgd, threads, target_seconds):
-    """One BOUNDED run of the reference on the bench scene, sized for about `target_seconds` of wall clock.  The rates the
+    """One BOUNDED run of the reference on the bench scene, sized for about `target_seconds` of rendering.  The rates the
     reference prints (paths / s, rays / s) do not depend on the film size or the sample count, so the sample is the same
     scene, camera and settings on a film scaled down (same aspect) until 1 spp fits the budget -- the full film at several
-    spp when that fits too.  Calibrated on a 1/8-size film; every run has a hard timeout, and if the sized run does not
-    finish the probe itself is the sample.  Returns (description, run)."""
+    spp when that fits too.  Calibrated on a 1/8-size film and re-sized once more if the first sized run turns out
+    shorter than a third of the target (the reference's clock ticks in 0.5 s steps: a short run gives a coarse rate);
+    every run has a hard timeout, and if a sized run does not finish the last finished one is the sample.
+    Returns (description "WxH at N spp", run)."""
     w, h = cfgd["film"]["width"], cfgd["film"]["height"]
     pw, ph = max(32, w // 8), max(18, h // 8)
     try:
-        probe = run_reference_once(with_film(cfgd, pw, ph), 1, threads, timeout=180)
+        run = run_reference_once(with_film(cfgd, pw, ph), 1, threads, timeout=180)
     except subprocess.TimeoutExpired:  # a pathologically slow host: a thumbnail, or give up (the caller reports it)
         pw, ph = 64, max(18, 64 * h // max(w, 1))
-        probe = run_reference_once(with_film(cfgd, pw, ph), 1, threads, timeout=300)
-        return f"{pw}x{ph} at 1 spp (the 1/8-size probe exceeded its time limit)", probe
-    rate = probe["paths"] / max(probe["wall_seconds"], 0.25)  # paths per second of wall clock, scene build included
-    budget = rate * target_seconds
-    if budget >= w * h:
-        sw, sh, spp = w, h, max(1, min(64, int(budget // (w * h))))
-    else:
-        f = max((budget / float(w * h)) ** 0.5, pw / float(w))
-        sw, sh, spp = max(pw, int(w * f)), max(ph, int(h * f)), 1
-    desc = f"{sw}x{sh} at {spp} spp"
-    if (sw, sh, spp) == (pw, ph, 1):
-        return desc, probe
-    try:
-        return desc, run_reference_once(with_film(cfgd, sw, sh), spp, threads, timeout=max(60.0, 5.0 * target_seconds))
-    except subprocess.TimeoutExpired:
-        return f"{pw}x{ph} at 1 spp (the sized run of {desc} exceeded its time limit)", probe
+        run = run_reference_once(with_film(cfgd, pw, ph), 1, threads, timeout=300)
+        return f"{pw}x{ph} at 1 spp (the 1/8-size probe exceeded its time limit)", run
+    desc = f"{pw}x{ph} at 1 spp"
+
+    def shape(n_paths):  # the film / spp that holds about n_paths camera paths
+        if n_paths >= w * h:
+            return w, h, max(1, min(256, int(n_paths // (w * h))))
+        f = max((n_paths / float(w * h)) ** 0.5, pw / float(w))
+        return max(pw, int(w * f)), max(ph, int(h * f)), 1
+
+    for _ in range(6):
+        secs = max(run["seconds"], 0.25)  # its own render clock: it ticks in 0.5 s steps (the polling loop of main())
+        if secs >= target_seconds / 3.0:
+            break
+        # below ~1 s the clock says nothing (one tick): grow geometrically; above, scale to the target
+        grow = 8.0 if secs < 1.1 else min(8.0, target_seconds / secs)
+        sw, sh, spp = shape(run["paths"] * grow)
+        new_desc = f"{sw}x{sh} at {spp} spp"
+        if new_desc == desc:
+            break
+        try:
+            run = run_reference_once(with_film(cfgd, sw, sh), spp, threads, timeout=max(60.0, 5.0 * target_seconds))
+            desc = new_desc
+        except subprocess.TimeoutExpired:
+            desc += f" (the sized run of {new_desc} exceeded its time limit)"
+            break
+    return desc, run
 
 
 def workload_name(args, w, h):
@@ -497,10 +537,9 @@ def main():
                              f"camera and settings; rates do not depend on film size), unmodified reference main() "
                              f"(tiled, 32x32 blocks, {threads} threads)"}
             if args.cpu_one_thread:  # the deterministic single-thread rate (no RNG race), on a reduced film
-                one = with_film(res["cfgd"], max(32, res["w"] // 16), max(18, res["h"] // 16))
-                r1 = run_reference_once(one, 1, 1, timeout=300)
+                d1, r1 = cpu_sample(res["cfgd"], 1, min(8.0, args.cpu_seconds))
                 cpu["one_thread"] = {"value": r1["mpaths_per_s"], "mrays_per_s": r1["mrays_per_s"],
-                                     "sample": f"{one['film']['width']}x{one['film']['height']} at 1 spp, 1 thread"}
+                                     "sample": f"film {d1}, 1 thread"}
         except Exception as e:  # the baseline is reported, never required
             cpu = {"value": None, "unit": "Mpaths/s", "cores": threads, "kind": "reference", "sample": f"failed: {e}"}
     value = res["paths"] / res["dev_s"] * 1e-6
