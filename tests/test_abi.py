@@ -85,3 +85,33 @@ def test_scene_errors():
         pt.Scene.from_json(bad, 32, 32, device=-1)
     with pytest.raises(pt.B200ptError):
         pt.Scene.from_json(dict(sj, instances=[]), 32, 32, device=-1)
+
+
+def test_config_device_keys():
+    """The scheduling keys this backend adds next to the reference's "threads": "devices": N, "device_ids": [...],
+    "async_render"; like "threads" they do not change the image.  Absent: one GPU, the paced mode."""
+    import pathtrace_b200 as pt
+    base = pt.default_config_dict()
+    c = pt.Config.from_json(base)
+    assert c.device_count <= 1 and c.async_render == 0 and c.device == 0
+    c = pt.Config.from_json(dict(base, devices=4))
+    assert c.device_count == 4 and list(c.device_ids)[:4] == [0, 1, 2, 3]
+    c = pt.Config.from_json(dict(base, device_ids=[2, 5, 7], async_render=True))
+    assert c.device_count == 3 and list(c.device_ids)[:3] == [2, 5, 7] and c.device == 2 and c.async_render == 1
+    for bad in (dict(devices=9), dict(device_ids=[]), dict(device_ids=list(range(9)))):
+        with pytest.raises(pt.B200ptError):
+            pt.Config.from_json(dict(base, **bad))
+    # Config.replace(devices=[...]) is the Python spelling
+    c = pt.Config.from_json(base).replace(devices=[1, 3])
+    assert c.device_count == 2 and list(c.device_ids)[:2] == [1, 3] and c.device == 1
+    assert pt.Config.from_json(base).replace(devices=[2]).device_count == 0
+
+
+def test_render_start_refuses_bad_device_lists_without_a_gpu():
+    """No device here: a multi-device render must fail with NO_DEVICE (never fall back), a one-device one likewise."""
+    import pathtrace_b200 as pt
+    scene = pt.Scene.from_file(scene_path("cornell_box"), 16, 16, device=-1)
+    cfg = pt.Config.from_json(pt.default_config_dict(width=16, height=16, samples=4, scene=scene_path("cornell_box")))
+    for c in (cfg.replace(device=-1), cfg.replace(devices=[0, 1])):
+        with pytest.raises(pt.B200ptError):
+            pt.renderer_from_config(scene, c).start_render()

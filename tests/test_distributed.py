@@ -59,3 +59,16 @@ def test_reduce_film_gloo_world2(tmp_path):
     counts = np.load(tmp_path / "counts.npy")
     assert np.all(film[..., 0] == sum(range(1, 11))) and np.all(film[..., 3] == 10)
     assert counts.tolist() == [10, 300]
+
+
+def test_render_sharded_raises_on_every_rank_when_samples_are_fewer_than_ranks():
+    """with config.samples < world_size only the empty ranks used to raise and the others hung in the reduce.
+    The check now comes before the sharding, so every rank raises -- and before any GPU work, so it can be tested here."""
+    import pathtrace_b200 as pt
+    from pathtrace_b200.distributed import render_sharded
+    from conftest import scene_path
+    scene = pt.Scene.from_file(scene_path("cornell_box"), 8, 8, device=-1)
+    cfg = pt.Config.from_json(pt.default_config_dict(width=8, height=8, samples=1, scene=scene_path("cornell_box")))
+    for rank in (0, 1):
+        with pytest.raises(ValueError, match="fewer samples than ranks"):
+            render_sharded(scene, cfg, rank, 2)
