@@ -28,12 +28,15 @@ __device__ __forceinline__ float4 f4(V3 a, float w) { return make_float4(a.x, a.
 
 // Block-wide queue reservation: every thread passes a bit mask of the NQ queues it appends to.  Ranks come from
 // warp ballots, warp totals are prefix-summed in shared memory and ONE atomicAdd per (block, queue) reserves the
-// range.  Must be called by all threads of the block.
+// range.  Must be called by all threads of the block.  Two barriers, not three: the scratch is double-buffered by
+// `phase` (the caller's loop iteration & 1) -- a thread that runs ahead into iteration i + 1 writes the other buffer,
+// and it cannot reach iteration i + 2 (this buffer again) before every thread has passed the first barrier of i + 1,
+// i.e. has finished reading iteration i's values.
 template <int NQ, int NW = kWarps>
-__device__ __forceinline__ void block_reserve(unsigned mask, int32_t *const (&counter)[NQ], int (&pos)[NQ])
+__device__ __forceinline__ void block_reserve(unsigned mask, int32_t *const (&counter)[NQ], int (&pos)[NQ], int phase)
 {
-    __shared__ int s_cnt[NQ][NW];
-    __shared__ int s_base[NQ];
+    __shared__ int s_cnt[2][NQ][NW];
+    __shared__ int s_base[2][NQ];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned lt = (1u << lane) - 1u;
     int rank[NQ];
@@ -42,24 +45,42 @@ __device__ __forceinline__ void block_reserve(unsigned mask, int32_t *const (&co
         unsigned b = __ballot_sync(0xffffffffu, (mask >> q) & 1u);
         rank[q] = __popc(b & lt);
         if (lane == 0)
-            s_cnt[q][warp] = __popc(b);
+            s_cnt[phase][q][warp] = __popc(b);
     }
     __syncthreads();
     if (threadIdx.x < NQ) {
         int total = 0;
 #pragma unroll
         for (int w = 0; w < NW; w++) {
-            int c = s_cnt[threadIdx.x][w];
-            s_cnt[threadIdx.x][w] = total;
+            int c = s_cnt[phase][threadIdx.x][w];
+            s_cnt[phase][threadIdx.x][w] = total;
             total += c;
         }
-        s_base[threadIdx.x] = total ? atomicAdd(counter[threadIdx.x], total) : 0;
+        s_base[phase][threadIdx.x] = total ? atomicAdd(counter[threadIdx.x], total) : 0;
     }
     __syncthreads();
 #pragma unroll
     for (int q = 0; q < NQ; q++)
-        pos[q] = s_base[q] + s_cnt[q][warp] + rank[q];
-    __syncthreads();
+        pos[q] = s_base[phase][q] + s_cnt[phase][q][warp] + rank[q];
+}
+
+// The same reservation per WARP: ranks from ballots, one atomicAdd per (warp, queue that gets entries), no barrier and no
+// shared memory -- a warp whose loads have arrived does not wait for the slowest warp of its block.  Eight times the
+// atomics of the block-wide form; the queue comes out in warp-sized runs instead of block-sized ones, which nothing
+// downstream cares about (BVH scenes sort their queues, and a run of 32 slots still shares its sectors).
+template <int NQ>
+__device__ __forceinline__ void warp_reserve(unsigned mask, int32_t *const (&counter)[NQ], int (&pos)[NQ])
+{
+    const int lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int q = 0; q < NQ; q++) {
+        const unsigned b = __ballot_sync(0xffffffffu, (mask >> q) & 1u);
+        int base = 0;
+        if (lane == 0 && b)
+            base = atomicAdd(counter[q], __popc(b));
+        pos[q] = __shfl_sync(0xffffffffu, base, 0) + __popc(b & lt);
+    }
 }
 
 // A small scene in shared memory: stage() copies boxes, instances and forward transforms and points the view at
@@ -239,7 +260,8 @@ __global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView
     const int32_t *q_in = bounce == 0 ? nullptr : wf.q_ext[bounce & 1];
     int32_t *const kind_counter[SK_COUNT] = {row + CNT_KIND0, row + CNT_KIND0 + 1, row + CNT_KIND0 + 2,
                                              row + CNT_KIND0 + 3, row + CNT_KIND0 + 4};
-    for (int base = blockIdx.x * kExtThreads; base < n; base += gridDim.x * kExtThreads) {
+    int phase = 0;
+    for (int base = blockIdx.x * kExtThreads; base < n; base += gridDim.x * kExtThreads, phase ^= 1) {
         const int i = base + threadIdx.x;
         unsigned mask = 0;
         int slot = 0;
@@ -275,7 +297,11 @@ __global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView
             mask = 1u << kind;
         }
         int pos[SK_COUNT];
-        block_reserve<SK_COUNT, kExtThreads / 32>(mask, kind_counter, pos);
+#ifdef PT_EXT_WARP_RESERVE
+        warp_reserve<SK_COUNT>(mask, kind_counter, pos);
+#else
+        block_reserve<SK_COUNT, kExtThreads / 32>(mask, kind_counter, pos, phase);
+#endif
         if (mask) {
             int kind = __ffs(mask) - 1;
             PT_CHECK(pos[kind] >= 0 && pos[kind] < wf.capacity);
@@ -298,7 +324,8 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
     int32_t *q_next = sorted ? wf.q_raw_ext : wf.q_ext[(bounce + 1) & 1];
     int32_t *q_nee_out = sorted ? wf.q_raw_nee : wf.q_nee;
     int32_t *const counter[2] = {row + CNT_NEE, row + CNT_ROW + CNT_EXT};
-    for (int base = blockIdx.x * kThreads; base < n; base += gridDim.x * kThreads) {
+    int phase = 0;
+    for (int base = blockIdx.x * kThreads; base < n; base += gridDim.x * kThreads, phase ^= 1) {
         const int i = base + threadIdx.x;
         unsigned mask = 0;
         int slot = 0;
@@ -395,7 +422,11 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
                 atomicAdd(row + CNT_NEE_SKIP, __popc(b));
         }
         int pos[2];
-        block_reserve<2>(mask, counter, pos);
+#ifdef PT_SHADE_BLOCK_RESERVE
+        block_reserve<2>(mask, counter, pos, phase);
+#else
+        warp_reserve<2>(mask, counter, pos); // ncu: the block-wide form's barriers were 33 % of k_shade's stall samples
+#endif
         PT_CHECK(!(mask & 1u) || (pos[0] >= 0 && pos[0] < wf.capacity));
         PT_CHECK(!(mask & 2u) || (pos[1] >= 0 && pos[1] < wf.capacity));
         if (mask & 1u) {
