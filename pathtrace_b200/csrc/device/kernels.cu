@@ -31,7 +31,9 @@ __device__ __forceinline__ float4 f4(V3 a, float w) { return make_float4(a.x, a.
 // range.  Must be called by all threads of the block.  Two barriers, not three: the scratch is double-buffered by
 // `phase` (the caller's loop iteration & 1) -- a thread that runs ahead into iteration i + 1 writes the other buffer,
 // and it cannot reach iteration i + 2 (this buffer again) before every thread has passed the first barrier of i + 1,
-// i.e. has finished reading iteration i's values.
+// i.e. has finished reading iteration i's values.  (Reserving per warp instead -- no barrier at all, one atomic per warp and
+// queue -- was measured in round 2 because barriers are a third of k_shade's stall samples: eight times the same-address
+// atomics saturate the L2 atomic unit, k_shade 100 -> 141 ms per book2_final step, 51 -> 89 ms on cornell_box.)
 template <int NQ, int NW = kWarps>
 __device__ __forceinline__ void block_reserve(unsigned mask, int32_t *const (&counter)[NQ], int (&pos)[NQ], int phase)
 {
@@ -62,25 +64,6 @@ __device__ __forceinline__ void block_reserve(unsigned mask, int32_t *const (&co
 #pragma unroll
     for (int q = 0; q < NQ; q++)
         pos[q] = s_base[phase][q] + s_cnt[phase][q][warp] + rank[q];
-}
-
-// The same reservation per WARP: ranks from ballots, one atomicAdd per (warp, queue that gets entries), no barrier and no
-// shared memory -- a warp whose loads have arrived does not wait for the slowest warp of its block.  Eight times the
-// atomics of the block-wide form; the queue comes out in warp-sized runs instead of block-sized ones, which nothing
-// downstream cares about (BVH scenes sort their queues, and a run of 32 slots still shares its sectors).
-template <int NQ>
-__device__ __forceinline__ void warp_reserve(unsigned mask, int32_t *const (&counter)[NQ], int (&pos)[NQ])
-{
-    const int lane = threadIdx.x & 31;
-    const unsigned lt = (1u << lane) - 1u;
-#pragma unroll
-    for (int q = 0; q < NQ; q++) {
-        const unsigned b = __ballot_sync(0xffffffffu, (mask >> q) & 1u);
-        int base = 0;
-        if (lane == 0 && b)
-            base = atomicAdd(counter[q], __popc(b));
-        pos[q] = __shfl_sync(0xffffffffu, base, 0) + __popc(b & lt);
-    }
 }
 
 // A small scene in shared memory: stage() copies boxes, instances and forward transforms and points the view at
@@ -297,11 +280,7 @@ __global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView
             mask = 1u << kind;
         }
         int pos[SK_COUNT];
-#ifdef PT_EXT_WARP_RESERVE
-        warp_reserve<SK_COUNT>(mask, kind_counter, pos);
-#else
         block_reserve<SK_COUNT, kExtThreads / 32>(mask, kind_counter, pos, phase);
-#endif
         if (mask) {
             int kind = __ffs(mask) - 1;
             PT_CHECK(pos[kind] >= 0 && pos[kind] < wf.capacity);
@@ -422,11 +401,7 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
                 atomicAdd(row + CNT_NEE_SKIP, __popc(b));
         }
         int pos[2];
-#ifdef PT_SHADE_BLOCK_RESERVE
         block_reserve<2>(mask, counter, pos, phase);
-#else
-        warp_reserve<2>(mask, counter, pos); // ncu: the block-wide form's barriers were 33 % of k_shade's stall samples
-#endif
         PT_CHECK(!(mask & 1u) || (pos[0] >= 0 && pos[0] < wf.capacity));
         PT_CHECK(!(mask & 2u) || (pos[1] >= 0 && pos[1] < wf.capacity));
         if (mask & 1u) {
