@@ -292,8 +292,12 @@ __global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView
 }
 
 // One instantiation per (shade queue, integrator): each holds the code of its own materials only.
+#ifndef PT_SHADE_THREADS
+#define PT_SHADE_THREADS 256
+#endif
+constexpr int kShadeThreads = PT_SHADE_THREADS;
 template <int kind, bool NEE, bool CORR>
-__global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
+__global__ void __launch_bounds__(kShadeThreads, 1024 / kShadeThreads) k_shade(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
     const long long sample_base = wf.ctl->sample_base;
     int32_t *row = wf.counters + bounce * CNT_ROW;
@@ -304,7 +308,7 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
     int32_t *q_nee_out = sorted ? wf.q_raw_nee : wf.q_nee;
     int32_t *const counter[2] = {row + CNT_NEE, row + CNT_ROW + CNT_EXT};
     int phase = 0;
-    for (int base = blockIdx.x * kThreads; base < n; base += gridDim.x * kThreads, phase ^= 1) {
+    for (int base = blockIdx.x * kShadeThreads; base < n; base += gridDim.x * kShadeThreads, phase ^= 1) {
         const int i = base + threadIdx.x;
         unsigned mask = 0;
         int slot = 0;
@@ -401,7 +405,7 @@ __global__ void __launch_bounds__(kThreads, 4) k_shade(PtSceneView s, RenderPara
                 atomicAdd(row + CNT_NEE_SKIP, __popc(b));
         }
         int pos[2];
-        block_reserve<2>(mask, counter, pos, phase);
+        block_reserve<2, kShadeThreads / 32>(mask, counter, pos, phase);
         PT_CHECK(!(mask & 1u) || (pos[0] >= 0 && pos[0] < wf.capacity));
         PT_CHECK(!(mask & 2u) || (pos[1] >= 0 && pos[1] < wf.capacity));
         if (mask & 1u) {
@@ -1073,11 +1077,11 @@ void launch_shade(const PtSceneView &s, const RenderParams &rp, const Wavefront 
 #define PT_LAUNCH_SHADE(K)                                                  \
     case K:                                                                 \
         if (rp.corrected)                                                          \
-            k_shade<K, false, true><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);  \
+            k_shade<K, false, true><<<lc.blocks * kThreads / kShadeThreads, kShadeThreads, 0, st>>>(s, rp, wf, bounce);  \
         else if (nee)                                                              \
-            k_shade<K, true, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce);  \
+            k_shade<K, true, false><<<lc.blocks * kThreads / kShadeThreads, kShadeThreads, 0, st>>>(s, rp, wf, bounce);  \
         else                                                                       \
-            k_shade<K, false, false><<<lc.blocks, kThreads, 0, st>>>(s, rp, wf, bounce); \
+            k_shade<K, false, false><<<lc.blocks * kThreads / kShadeThreads, kShadeThreads, 0, st>>>(s, rp, wf, bounce); \
         break;
     switch (kind) {
         PT_LAUNCH_SHADE(SK_MISS)
