@@ -201,7 +201,7 @@ def cpu_sample(cfgd, threads, target_seconds):
 
     for _ in range(6):
         secs = max(run["seconds"], 0.25)  # its own render clock: it ticks in 0.5 s steps (the polling loop of main())
-        if secs >= target_seconds / 3.0:
+        if secs >= 0.6 * target_seconds:  # long enough that a 0.5 s tick is a few per cent
             break
         # below ~1 s the clock says nothing (one tick): grow geometrically; above, scale to the target
         grow = 8.0 if secs < 1.1 else min(8.0, target_seconds / secs)
@@ -234,19 +234,21 @@ def reference_arm(args):
     w, h = cfgd["film"]["width"], cfgd["film"]["height"]
     t_arm = time.perf_counter()
     try:
-        desc, first = cpu_sample(cfgd, threads, 10.0)  # calibration + the first sample; doubles as the warm-up run
+        # a step of about 10 s (its 0.5 s clock tick is then ~5 %), shorter only if K steps would not fit the budget
+        step_target = max(3.0, min(10.0, 140.0 / max(1, args.steps)))
+        desc, first = cpu_sample(cfgd, threads, step_target)  # calibration + the first sample; doubles as the warm-up run
     except Exception as e:  # noqa: BLE001 -- the arm must end with a line and exit 0 whatever the host does
         print(json.dumps({"impl": "reference", "unavailable": f"reference CPU run failed or timed out: {e}"[:300]}), flush=True)
         return 0
     per_step = max(first["wall_seconds"], 0.5)
-    budget = 150.0  # seconds of timed runs, whatever --steps asks for
+    budget = 170.0  # seconds of timed runs, whatever --steps asks for
     steps = max(1, min(args.steps, int(budget / per_step)))
     warm = 1
     m = re.match(r"(\d+)x(\d+) at (\d+) spp", desc)
     sw, sh, spp = int(m.group(1)), int(m.group(2)), int(m.group(3))
     runs = []
     for _ in range(steps):
-        if runs and time.perf_counter() - t_arm > 240.0:
+        if runs and time.perf_counter() - t_arm > 270.0:
             break  # never let the arm run away
         try:
             runs.append(run_reference_once(with_film(cfgd, sw, sh), spp, threads, timeout=max(60.0, 6.0 * per_step)))
@@ -355,7 +357,8 @@ def load_peaks():
         with open(nc) as f:
             j = json.load(f)
         peaks["ncu"] = j.get("scenes", {})
-        peaks["ncu_source"] = f"profiles/ncu_metrics.json (ncu --set full, commit {j.get('commit', '?')})"
+        peaks["ncu_source"] = (f"profiles/ncu_metrics.json (ncu metrics pass over every launch of one warm batch, "
+                               f"tools/batch_profile.sh; commit {j.get('commit', '?')})")
     return peaks
 
 
