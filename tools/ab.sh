@@ -1,19 +1,19 @@
 #!/bin/bash
-# A/B of library variants on the GPU box: tools/ab.sh <scene> <variant suffixes...>  ("-" = the default build)
-# Variants are built with `make -C pathtrace_b200/csrc VARIANT=_x EXTRA=-D...`; each is benched twice, interleaved.
-SCENE=$1; shift
-mkdir -p gpurun_out
+# A/B of library builds on the GPU box: tools/ab.sh <tag> <steps> <scene> lib1.so lib2.so ...   (each lib is benched twice, interleaved)
+TAG=$1; STEPS=$2; SCENE=$3; shift 3
+OUT=gpurun_out; mkdir -p $OUT
 for rep in 1 2; do
-  for v in "$@"; do
-    sfx=$([ "$v" = "-" ] && echo "" || echo "_$v")
-    B200PT_LIB=pathtrace_b200/libb200pt$sfx.so python bench.py --scene $SCENE --steps 8 --warmup 3 --no-cpu-baseline \
-        > gpurun_out/ab_${SCENE}_${v}_$rep.json 2> gpurun_out/ab_err.log
-    python - "$SCENE" "$v" "$rep" <<'P'
-import json, sys
-sc, v, rep = sys.argv[1:]
-d = json.loads(open(f"gpurun_out/ab_{sc}_{v}_{rep}.json").read().strip().splitlines()[-1])
-r = d["roofline"]
-print(sc, v, rep, round(d["value"], 1), "e2e", round(d["e2e"]["value"], 1), r["kernel_ms"], "boxes/ray", round(r["boxes_per_ray"], 2))
-P
+  for lib in "$@"; do
+    name=$(basename $lib .so)
+    B200PT_LIB=$PWD/$lib python bench.py --scene $SCENE --steps $STEPS --warmup 3 --no-cpu-baseline > $OUT/${TAG}_${SCENE}_${name}_$rep.json 2> $OUT/${TAG}_${SCENE}_${name}_$rep.err || echo "FAILED $lib"
+    python - <<PY
+import json
+try:
+    j=json.loads(open("$OUT/${TAG}_${SCENE}_${name}_$rep.json").read().strip().splitlines()[-1])
+    k=j["roofline"]["kernel_ms"]
+    print("$name rep $rep: %.1f Mpaths/s  e2e %.1f  ms/step %.2f  kernels %s" % (j["value"], j["e2e"]["value"], j["ms_per_step"], {a: round(b,1) for a,b in k.items()}))
+except Exception as e:
+    print("$name rep $rep: no line", e)
+PY
   done
 done
