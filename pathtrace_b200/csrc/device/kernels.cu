@@ -26,6 +26,29 @@ constexpr int kWarps = kThreads / 32;
 __device__ __forceinline__ V3 xyz(float4 a) { return v3(a.x, a.y, a.z); }
 __device__ __forceinline__ float4 f4(V3 a, float w) { return make_float4(a.x, a.y, a.z, w); }
 
+// Path state is streamed: every record is read once and written once per bounce and the whole state (24 GB per batch) is far
+// beyond the L2, while the scene (1.6 MB for 8192 instances) is re-read by every ray.  The TRAVERSAL kernels therefore mark
+// their state accesses evict-first (ld.global.cs / st.global.cs), so that these do not push node and instance records out
+// of L1 / L2: k_extend -1.5 %, k_nee -1.1 % on book2_final.  The shade kernels do not: with the same hints k_shade is 8 %
+// slower (its records come back in the next kernel; measured, profiles/r2r_*).  PT_STATE_HINT is a bit mask for A/B builds:
+// 1 traversal loads, 2 traversal stores, 4 shade / raygen loads, 8 shade / raygen stores.
+#ifndef PT_STATE_HINT
+#define PT_STATE_HINT 3
+#endif
+template <bool TRAVERSAL = false> __device__ __forceinline__ float4 ld_state(const float4 *p)
+{
+    if (PT_STATE_HINT & (TRAVERSAL ? 1 : 4))
+        return __ldcs(p);
+    return *p;
+}
+template <bool TRAVERSAL = false> __device__ __forceinline__ void st_state(float4 *p, float4 v)
+{
+    if (PT_STATE_HINT & (TRAVERSAL ? 2 : 8))
+        __stcs(p, v);
+    else
+        *p = v;
+}
+
 // Block-wide queue reservation: every thread passes a bit mask of the NQ queues it appends to.  Ranks come from
 // warp ballots, warp totals are prefix-summed in shared memory and ONE atomicAdd per (block, queue) reserves the
 // range.  Must be called by all threads of the block.  Two barriers, not three: the scratch is double-buffered by
@@ -198,12 +221,12 @@ __global__ void __launch_bounds__(kThreads) k_raygen(PtSceneView s, RenderParams
         float v = (float)(j + (double)r.y) / (float)rp.height;
         V3 o, d;
         camera_ray(s.cam, u, v, r.z, r.w, o, d);
-        wf.ray[2 * slot] = f4(o, -1.f); // last_bsdf_pdf = -1 (integrator.h:183)
-        wf.ray[2 * slot + 1] = f4(d, 0.f);
-        wf.thr[2 * slot] = make_float4(1.f, 1.f, 1.f, 0.f);
-        wf.thr[2 * slot + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
-        wf.acc[2 * slot] = make_float4(0.f, 0.f, 0.f, 0.f); // whole 32-byte sectors: no read-modify-write in L2
-        wf.acc[2 * slot + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        st_state(&wf.ray[2 * slot], f4(o, -1.f)); // last_bsdf_pdf = -1 (integrator.h:183)
+        st_state(&wf.ray[2 * slot + 1], f4(d, 0.f));
+        st_state(&wf.thr[2 * slot], make_float4(1.f, 1.f, 1.f, 0.f));
+        st_state(&wf.thr[2 * slot + 1], make_float4(0.f, 0.f, 0.f, 0.f));
+        st_state(&wf.acc[2 * slot], make_float4(0.f, 0.f, 0.f, 0.f)); // whole 32-byte sectors: no read-modify-write in L2
+        st_state(&wf.acc[2 * slot + 1], make_float4(0.f, 0.f, 0.f, 0.f));
         if (wf.path_id) { // `random_double() < trace_probability` (renderer.h:652)
             int id = -1;
             if (rng4(key, stage_word(0, RNG_PATH_TRACE, 0), 0).x < wf.path_prob) {
@@ -257,7 +280,7 @@ __global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView
         if (live) {
             slot = q_in ? q_in[i] : i;
             PT_CHECK(slot >= 0 && slot < wf.capacity);
-            float4 ro = wf.ray[2 * slot], rd = wf.ray[2 * slot + 1];
+            float4 ro = ld_state<true>(&wf.ray[2 * slot]), rd = ld_state<true>(&wf.ray[2 * slot + 1]);
             mr.key = make_key(rp, wf, slot, sample_base);
             mr.stage = stage_word(bounce, RNG_EXT_MEDIUM, 0);
             T.init(xyz(ro), xyz(rd), 0.001f, PT_FLT_MAX);
@@ -267,14 +290,18 @@ __global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView
             if (live)
                 T.template run_small<COUNT, MEDIA>(s.small, s.inst, s.n_small, mr, &tc);
         } else {
-            T.template run_warp<COUNT, MEDIA>(s, live, mr, &tc); // all 32 lanes take part in the votes
+#ifdef PT_EXT_VOTE // A/B: the warp votes on the kind of the next step (the driver of rounds 1-2: 158.0 vs 156.6 ms per step)
+            T.template run_warp<COUNT, MEDIA>(s, live, mr, &tc);
+#else
+            T.template run_warp_nodes_first<COUNT, MEDIA>(s, live, mr, &tc); // all 32 lanes take part in the votes
+#endif
         }
         if (live) {
             Hit h;
             int kind = SK_MISS;
             if (T.template result<MEDIA>(s, h)) {
-                wf.hit[2 * slot] = f4(h.p, __int_as_float(h.inst | (h.face << kFaceShift)));
-                wf.hit[2 * slot + 1] = f4(h.n, h.t);
+                st_state<true>(&wf.hit[2 * slot], f4(h.p, __int_as_float(h.inst | (h.face << kFaceShift))));
+                st_state<true>(&wf.hit[2 * slot + 1], f4(h.n, h.t));
                 kind = shade_kind_of(s.mats[meta_material(s.inst[h.inst].meta)].kind);
             }
             mask = 1u << kind;
@@ -296,8 +323,11 @@ __global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView
 #define PT_SHADE_THREADS 256
 #endif
 constexpr int kShadeThreads = PT_SHADE_THREADS;
+#ifndef PT_SHADE_MINB
+#define PT_SHADE_MINB (1024 / PT_SHADE_THREADS) /* blocks per SM the register allocation aims at */
+#endif
 template <int kind, bool NEE, bool CORR>
-__global__ void __launch_bounds__(kShadeThreads, 1024 / kShadeThreads) k_shade(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
+__global__ void __launch_bounds__(kShadeThreads, PT_SHADE_MINB) k_shade(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
     const long long sample_base = wf.ctl->sample_base;
     int32_t *row = wf.counters + bounce * CNT_ROW;
@@ -322,29 +352,29 @@ __global__ void __launch_bounds__(kShadeThreads, 1024 / kShadeThreads) k_shade(P
                 // no ray direction, and a zero product -- a black sky -- leaves the sum alone: one 32-byte sector per miss
                 // instead of five.  (x + 0 == x for every x, NaN included; a NaN or infinite beta still gives a NaN product
                 // and is added, as in the reference.)
-                const float4 bt = wf.thr[2 * slot];
+                const float4 bt = ld_state(&wf.thr[2 * slot]);
                 const b200pt_texture &bg = s.tex[s.background];
                 V3 add;
                 if (bg.kind == B200PT_TEX_CONSTANT)
                     add = xyz(bt) * v3(bg.color[0], bg.color[1], bg.color[2]);
                 else
-                    add = shade_miss(s, xyz(wf.ray[2 * slot + 1]), xyz(bt));
+                    add = shade_miss(s, xyz(ld_state(&wf.ray[2 * slot + 1])), xyz(bt));
                 if (add.x != 0.f || add.y != 0.f || add.z != 0.f) {
-                    const float4 acc = wf.acc[2 * slot + 1];
-                    wf.acc[2 * slot + 1] = make_float4(acc.x + add.x, acc.y + add.y, acc.z + add.z, 0.f);
+                    const float4 acc = ld_state(&wf.acc[2 * slot + 1]);
+                    st_state(&wf.acc[2 * slot + 1], make_float4(acc.x + add.x, acc.y + add.y, acc.z + add.z, 0.f));
                 }
                 continue; // a miss never appends (every thread of the block takes the `continue` below)
             }
-            float4 ro = wf.ray[2 * slot], rd = wf.ray[2 * slot + 1], bt = wf.thr[2 * slot];
+            float4 ro = ld_state(&wf.ray[2 * slot]), rd = ld_state(&wf.ray[2 * slot + 1]), bt = ld_state(&wf.thr[2 * slot]);
             {
-                float4 hp = wf.hit[2 * slot], hn = wf.hit[2 * slot + 1];
+                float4 hp = ld_state(&wf.hit[2 * slot]), hn = ld_state(&wf.hit[2 * slot + 1]);
                 PathVertexIn in;
                 in.o = xyz(ro);
                 in.d = xyz(rd);
                 in.beta = xyz(bt);
                 in.last_bsdf_pdf = ro.w;
                 // only a light leaves `attenuation` as the previous vertex set it (material.h:187-191)
-                in.attenuation = kind == SK_LIGHT ? xyz(wf.thr[2 * slot + 1]) : v3(0.f, 0.f, 0.f);
+                in.attenuation = kind == SK_LIGHT ? xyz(ld_state(&wf.thr[2 * slot + 1])) : v3(0.f, 0.f, 0.f);
                 Hit rec;
                 rec.inst = __float_as_int(hp.w) & ((1 << kFaceShift) - 1);
                 rec.face = __float_as_int(hp.w) >> kFaceShift;
@@ -371,8 +401,8 @@ __global__ void __launch_bounds__(kShadeThreads, 1024 / kShadeThreads) k_shade(P
                 else
                     shade_hit_rpt<kind>(s, rp, in, rec, bounce, rnd, out);
                 if (out.add.x != 0.f || out.add.y != 0.f || out.add.z != 0.f) { // rare: the sum is read only then
-                    const float4 acc = wf.acc[2 * slot + 1];
-                    wf.acc[2 * slot + 1] = make_float4(acc.x + out.add.x, acc.y + out.add.y, acc.z + out.add.z, 0.f);
+                    const float4 acc = ld_state(&wf.acc[2 * slot + 1]);
+                    st_state(&wf.acc[2 * slot + 1], make_float4(acc.x + out.add.x, acc.y + out.add.y, acc.z + out.add.z, 0.f));
                 }
                 if (out.want_nee) {
                     // all lights below the horizon of this vertex: its light samples are all void (pt_shade.h), they
@@ -380,7 +410,7 @@ __global__ void __launch_bounds__(kShadeThreads, 1024 / kShadeThreads) k_shade(P
                     if (NEE && !CORR && lights_below_horizon(s, rec.p, rec.n)) {
                         nee_skipped = true;
                     } else {
-                        wf.acc[2 * slot] = f4(out.W, __int_as_float(out.mat_kind));
+                        st_state(&wf.acc[2 * slot], f4(out.W, __int_as_float(out.mat_kind)));
                         mask |= 1u;
                         if (sorted)
                             key_nee = sort_key_nee(s, rec.p);
@@ -389,10 +419,10 @@ __global__ void __launch_bounds__(kShadeThreads, 1024 / kShadeThreads) k_shade(P
                 if (out.cont) {
                     if (sorted)
                         key_ext = sort_key_ext(s, out.o, out.d);
-                    wf.ray[2 * slot] = f4(out.o, out.last_bsdf_pdf);
-                    wf.ray[2 * slot + 1] = f4(out.d, 0.f);
-                    wf.thr[2 * slot] = f4(out.beta, 0.f);
-                    wf.thr[2 * slot + 1] = f4(out.attenuation, 0.f);
+                    st_state(&wf.ray[2 * slot], f4(out.o, out.last_bsdf_pdf));
+                    st_state(&wf.ray[2 * slot + 1], f4(out.d, 0.f));
+                    st_state(&wf.thr[2 * slot], f4(out.beta, 0.f));
+                    st_state(&wf.thr[2 * slot + 1], f4(out.attenuation, 0.f));
                     mask |= 2u;
                 }
             }
@@ -474,7 +504,7 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
             PT_CHECK(q >= 0 && q < wf.counters[bounce * CNT_ROW + CNT_NEE] && q < wf.capacity);
             slot = wf.q_nee[q];
             PT_CHECK(slot >= 0 && slot < wf.capacity);
-            float4 hp = wf.hit[2 * slot], hn = wf.hit[2 * slot + 1], w = wf.acc[2 * slot];
+            float4 hp = ld_state<true>(&wf.hit[2 * slot]), hn = ld_state<true>(&wf.hit[2 * slot + 1]), w = ld_state<true>(&wf.acc[2 * slot]);
             RngKey key = make_key(rp, wf, slot, sample_base);
             nrays++;
             if (CORR)
@@ -671,7 +701,7 @@ __global__ void __launch_bounds__(kThreads) k_accumulate(RenderParams rp, Wavefr
             cq = film.csq[pix];
         }
         for (int k = 0; k < nsamp; k++) {
-            float4 v = wf.acc[2 * ((size_t)k * wf.npix + pix) + 1];
+            float4 v = ld_state(&wf.acc[2 * ((size_t)k * wf.npix + pix) + 1]);
             float x = is_nan(v.x) ? 0.f : v.x, y = is_nan(v.y) ? 0.f : v.y, z = is_nan(v.z) ? 0.f : v.z; // de_nan
             acc.x += x;
             acc.y += y;

@@ -491,6 +491,7 @@ struct Traversal {
         int32_t ref[4];
 #if defined(__CUDA_ARCH__)
         const float4 *q = reinterpret_cast<const float4 *>(node);
+        // (loading the node with the L1 evict-last priority, ld.global.nc.L1::evict_last, changes nothing: measured in round 2)
         const float4 lx = __ldg(q), ly = __ldg(q + 1), lz = __ldg(q + 2), hx = __ldg(q + 3), hy = __ldg(q + 4),
                      hz = __ldg(q + 5);
         const int4 r = __ldg(reinterpret_cast<const int4 *>(q + 6));
