@@ -244,6 +244,15 @@ __global__ void __launch_bounds__(kThreads) k_raygen(PtSceneView s, RenderParams
 
 // Small blocks: the queue reservation is a block-wide barrier, and a block waits for its slowest ray -- with 256
 // threads a quarter of all stall samples on the 8192-instance scene were that barrier.
+// the node phase of the walk ends when fewer than 1 / DIV of the warp's unfinished lanes want an inner node (0: when none does).
+// Measured on book2_final (profiles/r2n_ab_experiments.txt): DIV = 3 gains 0.3 %, 4 / 6 / 8 lose 0.4 - 1.5 % -- the policy is not
+// what limits the lanes of the node loop (14.7 of 32 in k_nee): the rays of a warp finish at different times.
+#ifndef PT_NEE_NODE_DIV
+#define PT_NEE_NODE_DIV 0
+#endif
+#ifndef PT_EXT_NODE_DIV
+#define PT_EXT_NODE_DIV 0
+#endif
 #ifndef PT_EXT_THREADS
 #define PT_EXT_THREADS 64
 #endif
@@ -293,7 +302,7 @@ __global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView
 #ifdef PT_EXT_VOTE // A/B: the warp votes on the kind of the next step (the driver of rounds 1-2: 158.0 vs 156.6 ms per step)
             T.template run_warp<COUNT, MEDIA>(s, live, mr, &tc);
 #else
-            T.template run_warp_nodes_first<COUNT, MEDIA>(s, live, mr, &tc); // all 32 lanes take part in the votes
+            T.template run_warp_nodes_first<COUNT, MEDIA, false, PT_EXT_NODE_DIV>(s, live, mr, &tc); // all 32 lanes take part
 #endif
         }
         if (live) {
@@ -527,7 +536,7 @@ __global__ void __launch_bounds__(kThreads, MEDIA ? PT_NEE_MEDIA_MINB : 4) k_nee
             if (trace)
                 T.template run_small<COUNT, MEDIA, ANY>(s.small, s.inst, s.n_small, mr, &tc);
         } else {
-            T.template run_warp_nodes_first<COUNT, MEDIA, ANY>(s, trace, mr, &tc);
+            T.template run_warp_nodes_first<COUNT, MEDIA, ANY, PT_NEE_NODE_DIV>(s, trace, mr, &tc);
         }
         if (trace && (!ANY || T.best_inst == lit)) {
             Hit lrec;

@@ -778,15 +778,36 @@ struct Traversal {
 #if defined(__CUDACC__)
     // while-while: inner nodes until no lane of the warp wants one any more, then the leaves that were reached,
     // together.  Same per-ray sequence of steps as run().
-    template <bool COUNT, bool MEDIA, bool ANY = false>
+    // DIV > 0: the node phase ends as soon as fewer than 1 / DIV of the unfinished lanes still want an inner node -- the
+    // many lanes waiting at their leaves are served first and the few stragglers walk on together with the lanes that
+    // pop their next node after the leaf (DIV = 2 is run_warp's vote, DIV = 0 the plain while-while).
+    template <bool COUNT, bool MEDIA, bool ANY = false, int DIV = 0>
     __device__ __forceinline__ void run_warp_nodes_first(const PtSceneView &s, bool active, const MediumRng &mr,
                                                          TraceCounters *counters)
     {
-        while (__any_sync(0xffffffffu, active)) {
-            while (__any_sync(0xffffffffu, active && cur >= 0))
+        if (DIV == 0) {
+            while (__any_sync(0xffffffffu, active)) {
+                while (__any_sync(0xffffffffu, active && cur >= 0))
+                    if (active && cur >= 0)
+                        active = node_step<COUNT, !ANY>(s, counters); // an occlusion query does not care for the order
+                if (active) // cur < 0 here
+                    active = leaf_step<COUNT, MEDIA, ANY>(s, mr, counters);
+            }
+            return;
+        }
+        while (true) {
+            unsigned m_act = __ballot_sync(0xffffffffu, active);
+            if (!m_act)
+                break;
+            while (true) {
+                const unsigned m_in = __ballot_sync(0xffffffffu, active && cur >= 0);
+                if (__popc(m_in) * DIV < __popc(m_act) || !m_in)
+                    break;
                 if (active && cur >= 0)
-                    active = node_step<COUNT, !ANY>(s, counters); // an occlusion query does not care for the order
-            if (active) // cur < 0 here
+                    active = node_step<COUNT, !ANY>(s, counters);
+                m_act = __ballot_sync(0xffffffffu, active);
+            }
+            if (active && cur < 0)
                 active = leaf_step<COUNT, MEDIA, ANY>(s, mr, counters);
         }
     }
