@@ -292,6 +292,12 @@ __global__ void __launch_bounds__(kExtThreads, PT_EXT_MINB) k_extend(PtSceneView
             float4 ro = ld_state<true>(&wf.ray[2 * slot]), rd = ld_state<true>(&wf.ray[2 * slot + 1]);
             mr.key = make_key(rp, wf, slot, sample_base);
             mr.stage = stage_word(bounce, RNG_EXT_MEDIUM, 0);
+            if (MEDIA) {
+                // the variates of media 0 and 1 now, with all lanes busy, instead of at the first medium leaf (k_extend -0.7 %
+                // on book2_final, whose mist every ray meets; the same in k_nee costs it 2 %: a sixth of its lanes are void)
+                mr.cached = rng4(mr.key, mr.stage, 0);
+                mr.cached_block = 0;
+            }
             T.init(xyz(ro), xyz(rd), 0.001f, PT_FLT_MAX);
             nrays++;
         }
