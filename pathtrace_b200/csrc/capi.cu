@@ -527,6 +527,8 @@ void enqueue_batch(Shard &r)
     launch_class(r, B200PT_K_RAYGEN, 1, [&] { pt::launch_raygen(s, r.rp, r.wf, r.lc, st); });
     const bool nee = r.cfg.integrator == B200PT_INTEGRATOR_INEEPT;
     const int n_bounces = nee ? r.cfg.max_bounces : r.cfg.max_bounces + 1;
+    if (n_bounces == 0) // the radiance sums are written by the bounce-0 shade kernels: with no bounce at all they are zero
+        CK(cudaMemsetAsync(r.wf.acc, 0, sizeof(float4) * 2 * (size_t)r.wf.capacity, st));
     for (int b = 0; b < n_bounces; b++) {
         launch_class(r, B200PT_K_EXTEND, 1, [&] { pt::launch_extend(s, r.rp, r.wf, b, r.lc, st); });
         // one launch per material kind the scene has (a queue of an absent kind stays empty)

@@ -223,10 +223,8 @@ __global__ void __launch_bounds__(kThreads) k_raygen(PtSceneView s, RenderParams
         camera_ray(s.cam, u, v, r.z, r.w, o, d);
         st_state(&wf.ray[2 * slot], f4(o, -1.f)); // last_bsdf_pdf = -1 (integrator.h:183)
         st_state(&wf.ray[2 * slot + 1], f4(d, 0.f));
-        st_state(&wf.thr[2 * slot], make_float4(1.f, 1.f, 1.f, 0.f));
-        st_state(&wf.thr[2 * slot + 1], make_float4(0.f, 0.f, 0.f, 0.f));
-        st_state(&wf.acc[2 * slot], make_float4(0.f, 0.f, 0.f, 0.f)); // whole 32-byte sectors: no read-modify-write in L2
-        st_state(&wf.acc[2 * slot + 1], make_float4(0.f, 0.f, 0.f, 0.f));
+        // throughput (1, 1, 1), no attenuation yet and an empty sum are what a camera vertex starts from: the bounce-0
+        // instantiations of k_shade (FIRST) know that and WRITE the sum, so none of the three is stored here
         if (wf.path_id) { // `random_double() < trace_probability` (renderer.h:652)
             int id = -1;
             if (rng4(key, stage_word(0, RNG_PATH_TRACE, 0), 0).x < wf.path_prob) {
@@ -341,7 +339,10 @@ constexpr int kShadeThreads = PT_SHADE_THREADS;
 #ifndef PT_SHADE_MINB
 #define PT_SHADE_MINB (1024 / PT_SHADE_THREADS) /* blocks per SM the register allocation aims at */
 #endif
-template <int kind, bool NEE, bool CORR>
+// FIRST: the camera vertices (bounce 0).  Every slot of the batch passes through exactly one of the FIRST kernels, with
+// throughput 1, no previous attenuation and an empty radiance sum: nothing of that is read, and the sum is stored (a whole
+// 32-byte sector with W) instead of read, added to and written back.
+template <int kind, bool NEE, bool CORR, bool FIRST>
 __global__ void __launch_bounds__(kShadeThreads, PT_SHADE_MINB) k_shade(PtSceneView s, RenderParams rp, Wavefront wf, int bounce)
 {
     const long long sample_base = wf.ctl->sample_base;
@@ -367,20 +368,24 @@ __global__ void __launch_bounds__(kShadeThreads, PT_SHADE_MINB) k_shade(PtSceneV
                 // no ray direction, and a zero product -- a black sky -- leaves the sum alone: one 32-byte sector per miss
                 // instead of five.  (x + 0 == x for every x, NaN included; a NaN or infinite beta still gives a NaN product
                 // and is added, as in the reference.)
-                const float4 bt = ld_state(&wf.thr[2 * slot]);
+                const float4 bt = FIRST ? make_float4(1.f, 1.f, 1.f, 0.f) : ld_state(&wf.thr[2 * slot]);
                 const b200pt_texture &bg = s.tex[s.background];
                 V3 add;
                 if (bg.kind == B200PT_TEX_CONSTANT)
                     add = xyz(bt) * v3(bg.color[0], bg.color[1], bg.color[2]);
                 else
                     add = shade_miss(s, xyz(ld_state(&wf.ray[2 * slot + 1])), xyz(bt));
-                if (add.x != 0.f || add.y != 0.f || add.z != 0.f) {
+                if (FIRST) {
+                    st_state(&wf.acc[2 * slot], make_float4(0.f, 0.f, 0.f, 0.f));
+                    st_state(&wf.acc[2 * slot + 1], make_float4(add.x, add.y, add.z, 0.f));
+                } else if (add.x != 0.f || add.y != 0.f || add.z != 0.f) {
                     const float4 acc = ld_state(&wf.acc[2 * slot + 1]);
                     st_state(&wf.acc[2 * slot + 1], make_float4(acc.x + add.x, acc.y + add.y, acc.z + add.z, 0.f));
                 }
                 continue; // a miss never appends (every thread of the block takes the `continue` below)
             }
-            float4 ro = ld_state(&wf.ray[2 * slot]), rd = ld_state(&wf.ray[2 * slot + 1]), bt = ld_state(&wf.thr[2 * slot]);
+            float4 ro = ld_state(&wf.ray[2 * slot]), rd = ld_state(&wf.ray[2 * slot + 1]);
+            const float4 bt = FIRST ? make_float4(1.f, 1.f, 1.f, 0.f) : ld_state(&wf.thr[2 * slot]);
             {
                 float4 hp = ld_state(&wf.hit[2 * slot]), hn = ld_state(&wf.hit[2 * slot + 1]);
                 PathVertexIn in;
@@ -389,7 +394,7 @@ __global__ void __launch_bounds__(kShadeThreads, PT_SHADE_MINB) k_shade(PtSceneV
                 in.beta = xyz(bt);
                 in.last_bsdf_pdf = ro.w;
                 // only a light leaves `attenuation` as the previous vertex set it (material.h:187-191)
-                in.attenuation = kind == SK_LIGHT ? xyz(ld_state(&wf.thr[2 * slot + 1])) : v3(0.f, 0.f, 0.f);
+                in.attenuation = kind == SK_LIGHT && !FIRST ? xyz(ld_state(&wf.thr[2 * slot + 1])) : v3(0.f, 0.f, 0.f);
                 Hit rec;
                 rec.inst = __float_as_int(hp.w) & ((1 << kFaceShift) - 1);
                 rec.face = __float_as_int(hp.w) >> kFaceShift;
@@ -415,10 +420,13 @@ __global__ void __launch_bounds__(kShadeThreads, PT_SHADE_MINB) k_shade(PtSceneV
                     shade_hit_ineept<kind>(s, rp, in, rec, rnd, out);
                 else
                     shade_hit_rpt<kind>(s, rp, in, rec, bounce, rnd, out);
-                if (out.add.x != 0.f || out.add.y != 0.f || out.add.z != 0.f) { // rare: the sum is read only then
+                if (FIRST) {
+                    st_state(&wf.acc[2 * slot + 1], make_float4(out.add.x, out.add.y, out.add.z, 0.f));
+                } else if (out.add.x != 0.f || out.add.y != 0.f || out.add.z != 0.f) { // rare: the sum is read only then
                     const float4 acc = ld_state(&wf.acc[2 * slot + 1]);
                     st_state(&wf.acc[2 * slot + 1], make_float4(acc.x + out.add.x, acc.y + out.add.y, acc.z + out.add.z, 0.f));
                 }
+                bool w_stored = false;
                 if (out.want_nee) {
                     // all lights below the horizon of this vertex: its light samples are all void (pt_shade.h), they
                     // are counted (k_tally) and never queued
@@ -426,11 +434,14 @@ __global__ void __launch_bounds__(kShadeThreads, PT_SHADE_MINB) k_shade(PtSceneV
                         nee_skipped = true;
                     } else {
                         st_state(&wf.acc[2 * slot], f4(out.W, __int_as_float(out.mat_kind)));
+                        w_stored = true;
                         mask |= 1u;
                         if (sorted)
                             key_nee = sort_key_nee(s, rec.p);
                     }
                 }
+                if (FIRST && !w_stored)
+                    st_state(&wf.acc[2 * slot], make_float4(0.f, 0.f, 0.f, 0.f)); // the other half of the sum's sector
                 if (out.cont) {
                     if (sorted)
                         key_ext = sort_key_ext(s, out.o, out.d);
@@ -1119,14 +1130,21 @@ void launch_shade(const PtSceneView &s, const RenderParams &rp, const Wavefront 
                   const LaunchCfg &lc, cudaStream_t st)
 {
     const bool nee = rp.integrator == B200PT_INTEGRATOR_INEEPT;
+#define PT_LAUNCH_SHADE_F(K, F)                                                     \
+    do {                                                                           \
+        if (rp.corrected)                                                          \
+            k_shade<K, false, true, F><<<lc.blocks * kThreads / kShadeThreads, kShadeThreads, 0, st>>>(s, rp, wf, bounce);  \
+        else if (nee)                                                              \
+            k_shade<K, true, false, F><<<lc.blocks * kThreads / kShadeThreads, kShadeThreads, 0, st>>>(s, rp, wf, bounce);  \
+        else                                                                       \
+            k_shade<K, false, false, F><<<lc.blocks * kThreads / kShadeThreads, kShadeThreads, 0, st>>>(s, rp, wf, bounce); \
+    } while (0)
 #define PT_LAUNCH_SHADE(K)                                                  \
     case K:                                                                 \
-        if (rp.corrected)                                                          \
-            k_shade<K, false, true><<<lc.blocks * kThreads / kShadeThreads, kShadeThreads, 0, st>>>(s, rp, wf, bounce);  \
-        else if (nee)                                                              \
-            k_shade<K, true, false><<<lc.blocks * kThreads / kShadeThreads, kShadeThreads, 0, st>>>(s, rp, wf, bounce);  \
+        if (bounce == 0)                                                           \
+            PT_LAUNCH_SHADE_F(K, true);                                            \
         else                                                                       \
-            k_shade<K, false, false><<<lc.blocks * kThreads / kShadeThreads, kShadeThreads, 0, st>>>(s, rp, wf, bounce); \
+            PT_LAUNCH_SHADE_F(K, false);                                           \
         break;
     switch (kind) {
         PT_LAUNCH_SHADE(SK_MISS)
@@ -1136,6 +1154,7 @@ void launch_shade(const PtSceneView &s, const RenderParams &rp, const Wavefront 
         PT_LAUNCH_SHADE(SK_ISOTROPIC)
     }
 #undef PT_LAUNCH_SHADE
+#undef PT_LAUNCH_SHADE_F
 }
 
 void launch_nee(const PtSceneView &s, const RenderParams &rp, const Wavefront &wf, int bounce, const LaunchCfg &lc,
