@@ -1,5 +1,5 @@
-"""BASELINE.json's FULL film sizes on the GPU -- the north-star target book2_final 3840 x 2160 and cornell_box 1024 x 1024 at the
-shipped integrator settings -- checked through properties that do not depend on the size, because the CPU restatement
+"""BASELINE.json's FULL film sizes on the GPU -- all five configs, from three_orbs 400 x 225 to the north-star target book2_final
+3840 x 2160, at the shipped integrator settings -- checked through properties that do not depend on the size, because the CPU restatement
 cannot render 8.3 M pixels in seconds:
 
   * a band of pixel rows of the full-size film against the CPU restatement, sample sum for sample sum (the restatement renders
@@ -22,8 +22,11 @@ pytestmark = pytest.mark.gpu
 
 FULL = [
     # scene, width, height, samples, rows of the band checked against the restatement
-    ("book2_final", 3840, 2160, 4, 2),
-    ("cornell_box", 1024, 1024, 8, 4),
+    ("book2_final", 3840, 2160, 4, 2),      # BASELINE.json configs[4], the north-star target
+    ("cornell_box", 1024, 1024, 8, 4),      # configs[1]
+    ("cornell_box_small_lights", 1024, 1024, 4, 4),  # configs[2]
+    ("cornell_box_with_volume", 1024, 1024, 4, 4),   # configs[3]
+    ("three_orbs", 400, 225, 8, 8),         # configs[0]
 ]
 
 
