@@ -32,6 +32,8 @@ struct BatchCtl {           // device-resident, advanced by the tally kernel at 
 struct Wavefront {
     // Per-slot state in PAIRS of float4 = one 32-byte DRAM sector per record: once the queues are sorted for ray
     // coherence a kernel visits slots in no particular order, and a 16-byte field on its own would cost a whole sector.
+    // k_raygen stores `ray` only: `thr` and `acc` of a slot are first written by the bounce-0 shade kernel the slot passes through
+    // (k_shade FIRST), which knows what a camera vertex starts from.
     float4 *ray; // [2 slot] = o.xyz, last_bsdf_pdf      [2 slot + 1] = d.xyz, -
     float4 *thr; // [2 slot] = beta.xyz, -               [2 slot + 1] = attenuation.xyz of the previous vertex, -
     float4 *hit; // [2 slot] = p.xyz, instance | face    [2 slot + 1] = n.xyz, t
